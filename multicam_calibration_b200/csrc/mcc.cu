@@ -1,0 +1,1185 @@
+// mcc.cu -- handle, host-side Levenberg-Marquardt driver and the C ABI of include/mcc.h.
+//
+// Host logic mirrors what the reference does around ceres::Solve:
+//   * parameter packing / unpacking : /root/reference/src/calibrator.cpp:36-71, 157-170, 251-283, 415-463
+//   * problem structure             : calibrator.cpp:353-370, 466-523 (one Huber(1.0) block per frame with >=1
+//                                     valid point of an active camera; constant intrinsic / extrinsic blocks)
+//   * trust-region loop             : Ceres' TrustRegionMinimizer + LevenbergMarquardtStrategy with the options of
+//                                     calibrator.cpp:300-305
+// All arithmetic of the solve runs in the kernels of kernels.cuh; the host only sequences launches, reads a
+// handful of scalars per iteration and takes the accept / reject decision.  There is no CPU fallback.
+#include "../../include/mcc.h"
+
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "kernels.cuh"
+
+namespace {
+
+using namespace mcc;
+
+double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+// ------------------------------------------------------------------------------------------------
+// NCCL, resolved at run time from the libnccl already loaded in the process (torch's) or the system one
+// ------------------------------------------------------------------------------------------------
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+enum { ncclSuccess_ = 0 };
+enum { ncclSum_ = 0, ncclMax_ = 2 };
+enum { ncclInt32_ = 2, ncclFloat64_ = 8 };
+struct NcclApi {
+  void* lib = nullptr;
+  int (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  int (*CommDestroy)(ncclComm_t) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  int (*GroupStart)() = nullptr;
+  int (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+  bool ok() const { return lib && GetUniqueId && CommInitRank && AllReduce && GroupStart && GroupEnd; }
+};
+NcclApi& nccl() {
+  static NcclApi api;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* n : names) {
+      api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+      if (api.lib) break;
+    }
+    if (api.lib) {
+      api.GetUniqueId = (int (*)(ncclUniqueId*))dlsym(api.lib, "ncclGetUniqueId");
+      api.CommInitRank = (int (*)(ncclComm_t*, int, ncclUniqueId, int))dlsym(api.lib, "ncclCommInitRank");
+      api.CommDestroy = (int (*)(ncclComm_t))dlsym(api.lib, "ncclCommDestroy");
+      api.AllReduce = (int (*)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t))dlsym(api.lib, "ncclAllReduce");
+      api.GroupStart = (int (*)())dlsym(api.lib, "ncclGroupStart");
+      api.GroupEnd = (int (*)())dlsym(api.lib, "ncclGroupEnd");
+      api.GetErrorString = (const char* (*)(int))dlsym(api.lib, "ncclGetErrorString");
+    }
+  }
+  return api;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host-side transforms
+// ------------------------------------------------------------------------------------------------
+// utils.h:29-39
+void h_rotation_matrix(const double* v, double* R) {
+  const double n = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+  double ang = 0.0, a[3] = {0.0, 0.0, 1.0};
+  if (n > 1e-8) { a[0] = v[0] / n; a[1] = v[1] / n; a[2] = v[2] / n; ang = n; }
+  const double s = std::sin(ang), c = std::cos(ang), k = 1.0 - c;
+  R[0] = k * a[0] * a[0] + c;        R[1] = k * a[0] * a[1] - s * a[2]; R[2] = k * a[0] * a[2] + s * a[1];
+  R[3] = k * a[0] * a[1] + s * a[2]; R[4] = k * a[1] * a[1] + c;        R[5] = k * a[1] * a[2] - s * a[0];
+  R[6] = k * a[0] * a[2] - s * a[1]; R[7] = k * a[1] * a[2] + s * a[0]; R[8] = k * a[2] * a[2] + c;
+}
+// calibrator.cpp:157-170: rotation block -> unit quaternion (largest-component branch) -> angle in [0,pi] * axis
+void h_transform_to_rvec_tvec(const double* T, double* out) {
+  const double m00 = T[0], m01 = T[1], m02 = T[2], m10 = T[4], m11 = T[5], m12 = T[6], m20 = T[8], m21 = T[9], m22 = T[10];
+  double qw, qx, qy, qz;
+  const double tr = m00 + m11 + m22;
+  if (tr > 0.0) {
+    const double t = std::sqrt(tr + 1.0), h = 0.5 / t;
+    qw = 0.5 * t; qx = (m21 - m12) * h; qy = (m02 - m20) * h; qz = (m10 - m01) * h;
+  } else if (m00 >= m11 && m00 >= m22) {
+    const double t = std::sqrt(m00 - m11 - m22 + 1.0), h = 0.5 / t;
+    qx = 0.5 * t; qw = (m21 - m12) * h; qy = (m10 + m01) * h; qz = (m20 + m02) * h;
+  } else if (m11 > m00 && m11 >= m22) {
+    const double t = std::sqrt(m11 - m22 - m00 + 1.0), h = 0.5 / t;
+    qy = 0.5 * t; qw = (m02 - m20) * h; qz = (m21 + m12) * h; qx = (m01 + m10) * h;
+  } else {
+    const double t = std::sqrt(m22 - m00 - m11 + 1.0), h = 0.5 / t;
+    qz = 0.5 * t; qw = (m10 - m01) * h; qx = (m02 + m20) * h; qy = (m12 + m21) * h;
+  }
+  double n = std::sqrt(qx * qx + qy * qy + qz * qz);
+  double ang = 0.0, ax = 1.0, ay = 0.0, az = 0.0;
+  if (n != 0.0) {
+    ang = 2.0 * std::atan2(n, std::fabs(qw));
+    if (qw < 0.0) n = -n;
+    ax = qx / n; ay = qy / n; az = qz / n;
+  }
+  out[0] = ax * ang; out[1] = ay * ang; out[2] = az * ang;
+  out[3] = T[3]; out[4] = T[7]; out[5] = T[11];
+}
+void h_rvec_tvec_to_transform(const double* in, double* T) {
+  double R[9];
+  h_rotation_matrix(in, R);
+  for (int i = 0; i < 3; i++) { T[i * 4 + 0] = R[i * 3 + 0]; T[i * 4 + 1] = R[i * 3 + 1]; T[i * 4 + 2] = R[i * 3 + 2]; T[i * 4 + 3] = in[3 + i]; }
+  T[12] = T[13] = T[14] = 0.0; T[15] = 1.0;
+}
+void h_mat4_mul(const double* A, const double* B, double* C) {
+  double t[16];
+  for (int i = 0; i < 4; i++)
+    for (int j = 0; j < 4; j++) t[i * 4 + j] = A[i * 4 + 0] * B[0 * 4 + j] + A[i * 4 + 1] * B[1 * 4 + j] + A[i * 4 + 2] * B[2 * 4 + j] + A[i * 4 + 3] * B[3 * 4 + j];
+  std::memcpy(C, t, sizeof(t));
+}
+// 4x4 inverse (Gauss-Jordan, partial pivoting)
+void h_mat4_inv(const double* A, double* Ai) {
+  double a[4][8];
+  for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) { a[i][j] = A[i * 4 + j]; a[i][4 + j] = i == j ? 1.0 : 0.0; }
+  for (int c = 0; c < 4; c++) {
+    int p = c;
+    for (int r = c + 1; r < 4; r++) if (std::fabs(a[r][c]) > std::fabs(a[p][c])) p = r;
+    if (p != c) for (int j = 0; j < 8; j++) std::swap(a[c][j], a[p][j]);
+    const double d = 1.0 / a[c][c];
+    for (int j = 0; j < 8; j++) a[c][j] *= d;
+    for (int r = 0; r < 4; r++) if (r != c) { const double f = a[r][c]; if (f != 0.0) for (int j = 0; j < 8; j++) a[r][j] -= f * a[c][j]; }
+  }
+  for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) Ai[i * 4 + j] = a[i][4 + j];
+}
+
+struct CamHost {
+  int model = 0, n_intr = 4, n_dist = 4;
+  double intr[4] = {0, 0, 0, 0}, dist[MCC_MAX_DIST] = {0, 0, 0, 0, 0, 0, 0, 0}, T[16];
+  int fix_intr = 0, fix_extr = 0, active = 1;
+  int nparam() const { return n_intr + n_dist; }
+};
+
+// device buffer that only grows
+template <typename T>
+struct DBuf {
+  T* p = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t n) {
+    if (n <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    cudaError_t e = cudaMalloc((void**)&p, std::max<size_t>(n, 1) * sizeof(T));
+    if (e == cudaSuccess) cap = n;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+template <typename T>
+struct PinBuf {
+  T* p = nullptr;
+  size_t cap = 0;
+  bool reserve(size_t n, size_t keep = 0) {
+    if (n <= cap) return true;
+    size_t ncap = std::max(n, cap + cap / 2);
+    T* q = nullptr;
+    if (cudaHostAlloc((void**)&q, std::max<size_t>(ncap, 1) * sizeof(T), cudaHostAllocDefault) != cudaSuccess) {
+      cudaGetLastError();
+      // no CUDA runtime / device: plain memory keeps the host-side API (add / get / set) usable
+      q = (T*)std::malloc(std::max<size_t>(ncap, 1) * sizeof(T));
+      if (!q) return false;
+      pinned = false;
+    }
+    if (p && keep) std::memcpy(q, p, keep * sizeof(T));
+    release();
+    p = q; cap = ncap;
+    return true;
+  }
+  void release() { if (p) { if (pinned) cudaFreeHost(p); else std::free(p); } p = nullptr; cap = 0; }
+  bool pinned = true;
+};
+
+void parallel_memcpy(void* dst, const void* src, size_t bytes) {
+  const size_t kMin = 8u << 20;
+  unsigned nt = std::min<unsigned>(8, std::max<unsigned>(1, std::thread::hardware_concurrency()));
+  if (bytes < 2 * kMin || nt <= 1) { std::memcpy(dst, src, bytes); return; }
+  nt = (unsigned)std::min<size_t>(nt, bytes / kMin);
+  std::vector<std::thread> th;
+  const size_t per = (bytes + nt - 1) / nt;
+  for (unsigned i = 0; i < nt; i++) {
+    const size_t o = i * per;
+    if (o >= bytes) break;
+    const size_t n = std::min(per, bytes - o);
+    th.emplace_back([=] { std::memcpy((char*)dst + o, (const char*)src + o, n); });
+  }
+  for (auto& t : th) t.join();
+}
+
+// AoS -> SoA on the device (observations arrive as Point3 / Point2 arrays, types.h:17-47)
+__global__ void k_aos_to_soa(size_t n, const double* __restrict__ w, const double* __restrict__ im, double* __restrict__ X,
+                             double* __restrict__ Y, double* __restrict__ Z, double* __restrict__ U, double* __restrict__ V) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  X[i] = w[3 * i]; Y[i] = w[3 * i + 1]; Z[i] = w[3 * i + 2];
+  U[i] = im[2 * i]; V[i] = im[2 * i + 1];
+}
+
+}  // namespace
+
+// =================================================================================================
+struct mcc_handle {
+  // ---- host problem (what Calibrator keeps, calibrator.h:42-48)
+  std::vector<CamHost> cams;
+  bool fix_all = false;
+  std::vector<int> npts;               // [F * ncam]
+  PinBuf<double> world, image;         // AoS staging: 3N, 2N
+  std::vector<double> poses;           // 16 F
+  std::vector<uint8_t> mask;           // N
+  size_t nobs = 0;
+  int nframes = 0;
+  std::vector<double> params;          // calibrator.cpp:36-46 layout
+  bool params_valid = false;
+  std::string err;
+  int device = -1;
+
+  // ---- structure (rebuilt when cameras / flags / frames / masks change)
+  bool structure_dirty = true, obs_dirty = true, mask_dirty = true, params_dirty = true;
+  int C_full = 0, C = 0, E = 0, nslots = 0, ntiles = 0, ngroups = 0, gstride = 0, rowstride = 0, npairs = 0, LD = 0;
+  std::vector<int> intr_off, ext_off, cam_col, col_param, slot_frame, frame_slot;
+  std::vector<size_t> group_obs0;      // [F*ncam] observation offset
+  long long nres = 0;
+
+  // ---- device
+  cudaStream_t stream = nullptr;
+  DBuf<double> d_aos_w, d_aos_i, d_X, d_Y, d_Z, d_U, d_V, d_res;
+  DBuf<uint8_t> d_mask;
+  DBuf<Tile> d_tiles;
+  DBuf<int> d_gto, d_lut, d_col_param, d_fail;
+  DBuf<CamMeta> d_cams;
+  DBuf<CcEntry> d_cc;
+  DBuf<int2> d_colmap;
+  DBuf<double> d_camp[2], d_pose[2];   // current / candidate
+  int cur = 0;
+  DBuf<double> d_setup, d_G, d_tile_s, d_Hff, d_gf, d_Hfc, d_Lf, d_cost_f, d_gmax_f, d_xn2_f, d_newcost_f, d_mcc_f, d_dx2_f, d_xn2c_f;
+  DBuf<double> d_cc_part, d_cc_sum, d_Hcc, d_gc, d_scale_c, d_scale_f, d_S_part, d_S_sum, d_M, d_yc, d_ysc, d_scal;
+  double* h_scal = nullptr;            // pinned mirror of d_scal
+  int* h_fail = nullptr;
+  int asm_grid = 0, sy_gx = 0, sy_gy = 0;
+  bool attrs_set = false;
+  long long launches = 0, h2d = 0, d2h = 0;
+
+  // ---- comm
+  ncclComm_t comm = nullptr;
+  int nranks = 1, rank = 0;
+
+  int ncam() const { return (int)cams.size(); }
+};
+
+namespace {
+
+mcc_status fail(mcc_handle* h, mcc_status st, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (h) h->err = buf;
+  return st;
+}
+#define CU(call)                                                                                         \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess) return fail(h, MCC_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+#define ST(call)                       \
+  do {                                 \
+    mcc_status s_ = (call);            \
+    if (s_ != MCC_OK) return s_;       \
+  } while (0)
+#define NC(call)                                                                                                      \
+  do {                                                                                                                \
+    int r_ = (call);                                                                                                  \
+    if (r_ != 0) return fail(h, MCC_ERR_NCCL, "%s failed: %s", #call, nccl().GetErrorString ? nccl().GetErrorString(r_) : "?"); \
+  } while (0)
+
+mcc_status ensure_device(mcc_handle* h) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return fail(h, MCC_ERR_NO_DEVICE, "no CUDA device available (%s); this library has no CPU fallback", e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+  }
+  if (h->device < 0) CU(cudaGetDevice(&h->device));
+  CU(cudaSetDevice(h->device));
+  if (!h->stream) CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  if (!h->h_scal) CU(cudaHostAlloc((void**)&h->h_scal, 32 * sizeof(double), cudaHostAllocDefault));
+  if (!h->h_fail) CU(cudaHostAlloc((void**)&h->h_fail, sizeof(int), cudaHostAllocDefault));
+  if (!h->attrs_set) {
+    CU(cudaFuncSetAttribute(k_tile_normal, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(k_schur_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(k_solve_cam, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(k_frame_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    h->attrs_set = true;
+  }
+  return MCC_OK;
+}
+
+// calibrator.cpp:251-283
+void init_params(mcc_handle* h) {
+  std::vector<double>& p = h->params;
+  p.clear();
+  for (const CamHost& c : h->cams) {
+    p.insert(p.end(), c.intr, c.intr + c.n_intr);
+    p.insert(p.end(), c.dist, c.dist + c.n_dist);
+  }
+  double prev[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+  for (int k = 1; k < h->ncam(); k++) {
+    double Tn0[16], rt[6];
+    h_mat4_mul(h->cams[k].T, prev, Tn0);
+    h_transform_to_rvec_tvec(Tn0, rt);
+    p.insert(p.end(), rt, rt + 6);
+    std::memcpy(prev, Tn0, sizeof(prev));
+  }
+  for (int f = 0; f < h->nframes; f++) {
+    double rt[6];
+    h_transform_to_rvec_tvec(&h->poses[16 * (size_t)f], rt);
+    p.insert(p.end(), rt, rt + 6);
+  }
+  h->params_valid = true;
+  h->params_dirty = true;
+}
+
+int tri_index(int bi, int bj, int nb) { return bi * nb - bi * (bi - 1) / 2 + (bj - bi); }
+
+// Everything that depends on cameras, flags, frame list and masks: reduced column maps
+// (calibrator.cpp:510-521), frames with residual blocks (calibrator.cpp:482-485), tiles.
+mcc_status build_structure(mcc_handle* h) {
+  const int ncam = h->ncam();
+  const int F = h->nframes;
+  h->intr_off.assign(ncam, 0); h->ext_off.assign(ncam, -1);
+  int off = 0;
+  for (int k = 0; k < ncam; k++) { h->intr_off[k] = off; off += h->cams[k].nparam(); }
+  for (int k = 1; k < ncam; k++) { h->ext_off[k] = off; off += 6; }
+  h->C_full = off;
+  h->cam_col.assign(h->C_full, -1);
+  h->col_param.clear();
+  for (int k = 0; k < ncam; k++)
+    if (!(h->fix_all || h->cams[k].fix_intr))
+      for (int j = 0; j < h->cams[k].nparam(); j++) { h->cam_col[h->intr_off[k] + j] = (int)h->col_param.size(); h->col_param.push_back(h->intr_off[k] + j); }
+  for (int k = 1; k < ncam; k++)
+    if (!h->cams[k].fix_extr)
+      for (int j = 0; j < 6; j++) { h->cam_col[h->ext_off[k] + j] = (int)h->col_param.size(); h->col_param.push_back(h->ext_off[k] + j); }
+  h->C = (int)h->col_param.size();
+  const int C = h->C;
+
+  // camera metadata + Gram lookup tables
+  std::vector<CamMeta> cm(ncam);
+  std::vector<int> lut((size_t)ncam * MAXC * MAXC, 0);
+  int max_nb = 1, max_nblk = 1;
+  for (int k = 0; k < ncam; k++) {
+    const CamHost& c = h->cams[k];
+    CamMeta& m = cm[k];
+    std::memset(&m, 0, sizeof(m));
+    m.model = c.model; m.nd = c.n_dist; m.intr_off = h->intr_off[k]; m.ext_off = h->ext_off[k];
+    m.ext_col = (k > 0) ? 4 + c.n_dist : -1;
+    m.pose_col = 4 + c.n_dist + (k > 0 ? 6 : 0);
+    m.r_col = m.pose_col + 6;
+    m.ncols = m.r_col + 1;
+    m.nb = (m.ncols + 2) / 3;
+    m.nblk = m.nb * (m.nb + 1) / 2;
+    m.active = c.active;
+    for (int j = 0; j < MAXCAMCOLS; j++) m.red_col[j] = -1;
+    for (int j = 0; j < c.nparam(); j++) m.red_col[j] = h->cam_col[h->intr_off[k] + j];
+    if (k > 0) for (int j = 0; j < 6; j++) m.red_col[m.ext_col + j] = h->cam_col[h->ext_off[k] + j];
+    m.lut_off = k * MAXC * MAXC;
+    for (int i = 0; i < m.ncols; i++)
+      for (int j = 0; j < m.ncols; j++) {
+        const int bi = i / 3, bj = j / 3;
+        int o;
+        if (bi <= bj) o = tri_index(bi, bj, m.nb) * 9 + (i % 3) * 3 + (j % 3);
+        else o = tri_index(bj, bi, m.nb) * 9 + (j % 3) * 3 + (i % 3);
+        lut[m.lut_off + i * MAXC + j] = o;
+      }
+    if (c.active) { max_nb = std::max(max_nb, m.nb); max_nblk = std::max(max_nblk, m.nblk); }
+  }
+  h->gstride = 9 * max_nblk;
+  h->rowstride = 3 * max_nb;
+  if (h->rowstride % 2 == 0) h->rowstride++;
+
+  // reduced column -> (camera, local column)
+  std::vector<int2> colmap(std::max(C, 1));
+  for (int k = 0; k < ncam; k++) {
+    const int ncc = cm[k].pose_col;   // intrinsic + extrinsic local columns
+    for (int j = 0; j < ncc; j++) if (cm[k].red_col[j] >= 0) colmap[cm[k].red_col[j]] = make_int2(k, j);
+  }
+  // camera-camera entries
+  std::vector<CcEntry> cc;
+  for (int k = 0; k < ncam; k++) {
+    if (!h->cams[k].active) continue;
+    const int ncc = cm[k].pose_col;
+    for (int i = 0; i < ncc; i++) {
+      if (cm[k].red_col[i] < 0) continue;
+      for (int j = i; j < ncc; j++) {
+        if (cm[k].red_col[j] < 0) continue;
+        cc.push_back(CcEntry{k, lut[cm[k].lut_off + i * MAXC + j], cm[k].red_col[i], cm[k].red_col[j]});
+      }
+      cc.push_back(CcEntry{k, lut[cm[k].lut_off + i * MAXC + cm[k].r_col], cm[k].red_col[i], -1});
+    }
+  }
+  h->E = (int)cc.size();
+
+  // observation offsets, active frames, tiles
+  h->group_obs0.assign((size_t)F * ncam + 1, 0);
+  {
+    size_t o = 0;
+    for (size_t g = 0; g < (size_t)F * ncam; g++) { h->group_obs0[g] = o; o += h->npts[g]; }
+    h->group_obs0[(size_t)F * ncam] = o;
+  }
+  h->slot_frame.clear();
+  h->frame_slot.assign(F, -1);
+  h->nres = 0;
+  for (int f = 0; f < F; f++) {
+    long long nv = 0;
+    for (int k = 0; k < ncam; k++) {
+      if (!h->cams[k].active) continue;
+      const size_t o0 = h->group_obs0[(size_t)f * ncam + k], n = h->npts[(size_t)f * ncam + k];
+      for (size_t i = 0; i < n; i++) nv += h->mask[o0 + i] != 0;
+    }
+    if (nv > 0) { h->frame_slot[f] = (int)h->slot_frame.size(); h->slot_frame.push_back(f); h->nres += 2 * nv; }
+  }
+  h->nslots = (int)h->slot_frame.size();
+  h->ngroups = h->nslots * ncam;
+  std::vector<Tile> tiles;
+  std::vector<int> gto((size_t)h->ngroups + 1, 0);
+  const int chunks_per_tile = TILE_OBS / 32;
+  for (int s = 0; s < h->nslots; s++) {
+    const int f = h->slot_frame[s];
+    for (int k = 0; k < ncam; k++) {
+      gto[(size_t)s * ncam + k] = (int)tiles.size();
+      const int n = h->npts[(size_t)f * ncam + k];
+      if (!h->cams[k].active || n == 0) continue;
+      const size_t o0 = h->group_obs0[(size_t)f * ncam + k];
+      if (o0 + n > 0x7fffffffull) return fail(h, MCC_ERR_TOO_LARGE, "more than 2^31 observations on one device");
+      const int nchunks = (n + 31) / 32;
+      const int nt = (nchunks + chunks_per_tile - 1) / chunks_per_tile;
+      const int base = nchunks / nt, rem = nchunks % nt;
+      int done = 0;
+      for (int t = 0; t < nt; t++) {
+        const int cnt = std::min(n - done, (base + (t < rem ? 1 : 0)) * 32);
+        tiles.push_back(Tile{(int)(o0 + done), cnt, s * ncam + k});
+        done += cnt;
+      }
+    }
+  }
+  gto[h->ngroups] = (int)tiles.size();
+  h->ntiles = (int)tiles.size();
+
+  const int NT = (C + 1 + SY_T - 1) / SY_T;
+  h->npairs = NT * (NT + 1) / 2;
+  h->LD = NT * SY_T;
+  h->sy_gy = (h->npairs + SY_THREADS - 1) / SY_THREADS;
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, h->device));
+  const int sms = prop.multiProcessorCount;
+  h->sy_gx = std::max(1, std::min((h->nslots + SY_FB - 1) / SY_FB, std::max(1, (2 * sms) / h->sy_gy)));
+  h->asm_grid = std::max(1, std::min(h->nslots, 4 * sms));
+
+  // upload structure
+  auto up = [&](auto& buf, const auto& vec) -> cudaError_t {
+    cudaError_t e = buf.reserve(vec.size());
+    if (e != cudaSuccess) return e;
+    if (vec.empty()) return cudaSuccess;
+    h->h2d += vec.size() * sizeof(vec[0]);
+    return cudaMemcpyAsync(buf.p, vec.data(), vec.size() * sizeof(vec[0]), cudaMemcpyHostToDevice, h->stream);
+  };
+  CU(up(h->d_cams, cm));
+  CU(up(h->d_lut, lut));
+  CU(up(h->d_colmap, colmap));
+  CU(up(h->d_cc, cc));
+  CU(up(h->d_tiles, tiles));
+  CU(up(h->d_gto, gto));
+  CU(up(h->d_col_param, h->col_param));
+  const size_t ns = std::max(h->nslots, 1);
+  CU(h->d_setup.reserve((size_t)std::max(h->ngroups, 1) * SETUP_STRIDE));
+  CU(h->d_G.reserve((size_t)std::max(h->ntiles, 1) * h->gstride));
+  CU(h->d_tile_s.reserve(std::max(h->ntiles, 1)));
+  CU(h->d_Hff.reserve(ns * 36)); CU(h->d_gf.reserve(ns * 6)); CU(h->d_Hfc.reserve(ns * 6 * std::max(C, 1))); CU(h->d_Lf.reserve(ns * 36));
+  CU(h->d_cost_f.reserve(ns)); CU(h->d_gmax_f.reserve(ns)); CU(h->d_xn2_f.reserve(ns)); CU(h->d_newcost_f.reserve(ns));
+  CU(h->d_mcc_f.reserve(ns)); CU(h->d_dx2_f.reserve(ns)); CU(h->d_xn2c_f.reserve(ns));
+  CU(h->d_cc_part.reserve((size_t)h->asm_grid * std::max(h->E, 1))); CU(h->d_cc_sum.reserve(std::max(h->E, 1)));
+  CU(h->d_Hcc.reserve((size_t)std::max(C, 1) * std::max(C, 1))); CU(h->d_gc.reserve(std::max(C, 1)));
+  CU(h->d_scale_c.reserve(std::max(C, 1))); CU(h->d_scale_f.reserve(ns * 6));
+  CU(h->d_S_part.reserve((size_t)h->sy_gx * h->npairs * SY_T * SY_T)); CU(h->d_S_sum.reserve((size_t)h->npairs * SY_T * SY_T));
+  CU(h->d_M.reserve((size_t)(C + 1) * std::max(C, 1))); CU(h->d_yc.reserve(std::max(C, 1))); CU(h->d_ysc.reserve(std::max(C, 1)));
+  CU(h->d_scal.reserve(32)); CU(h->d_fail.reserve(1));
+  for (int i = 0; i < 2; i++) { CU(h->d_camp[i].reserve(std::max(h->C_full, 1))); CU(h->d_pose[i].reserve(ns * 6)); }
+  CU(cudaStreamSynchronize(h->stream));   // the staging vectors above die with this scope
+  h->structure_dirty = false;
+  h->params_dirty = true;
+  return MCC_OK;
+}
+
+mcc_status upload_obs(mcc_handle* h) {
+  const size_t n = h->nobs;
+  if (h->obs_dirty) {
+    CU(h->d_aos_w.reserve(3 * n)); CU(h->d_aos_i.reserve(2 * n));
+    CU(h->d_X.reserve(n)); CU(h->d_Y.reserve(n)); CU(h->d_Z.reserve(n)); CU(h->d_U.reserve(n)); CU(h->d_V.reserve(n));
+    if (n) {
+      CU(cudaMemcpyAsync(h->d_aos_w.p, h->world.p, 3 * n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+      CU(cudaMemcpyAsync(h->d_aos_i.p, h->image.p, 2 * n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+      h->h2d += 5 * n * sizeof(double);
+      k_aos_to_soa<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(n, h->d_aos_w.p, h->d_aos_i.p, h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p);
+      h->launches++;
+      CU(cudaGetLastError());
+    }
+    h->obs_dirty = false;
+  }
+  if (h->mask_dirty) {
+    CU(h->d_mask.reserve(n));
+    if (n) { CU(cudaMemcpyAsync(h->d_mask.p, h->mask.data(), n, cudaMemcpyHostToDevice, h->stream)); h->h2d += n; }
+    h->mask_dirty = false;
+  }
+  return MCC_OK;
+}
+
+mcc_status upload_params(mcc_handle* h) {
+  if (!h->params_dirty) return MCC_OK;
+  h->cur = 0;
+  if (h->C_full) CU(cudaMemcpyAsync(h->d_camp[0].p, h->params.data(), h->C_full * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  std::vector<double> pose((size_t)h->nslots * 6);
+  for (int s = 0; s < h->nslots; s++) std::memcpy(&pose[(size_t)s * 6], &h->params[h->C_full + 6 * (size_t)h->slot_frame[s]], 6 * sizeof(double));
+  if (h->nslots) CU(cudaMemcpyAsync(h->d_pose[0].p, pose.data(), pose.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  h->h2d += (h->C_full + pose.size()) * sizeof(double);
+  CU(cudaStreamSynchronize(h->stream));
+  h->params_dirty = false;
+  return MCC_OK;
+}
+
+mcc_status download_params(mcc_handle* h) {
+  if (h->C_full) CU(cudaMemcpyAsync(h->params.data(), h->d_camp[h->cur].p, h->C_full * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  std::vector<double> pose((size_t)h->nslots * 6);
+  if (h->nslots) CU(cudaMemcpyAsync(pose.data(), h->d_pose[h->cur].p, pose.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  h->d2h += (h->C_full + pose.size()) * sizeof(double);
+  for (int s = 0; s < h->nslots; s++) std::memcpy(&h->params[h->C_full + 6 * (size_t)h->slot_frame[s]], &pose[(size_t)s * 6], 6 * sizeof(double));
+  return MCC_OK;
+}
+
+mcc_status prepare(mcc_handle* h) {
+  if (h->cams.empty() || h->nframes == 0) return fail(h, MCC_ERR_NO_DATA, "no data to run on!");
+  ST(ensure_device(h));
+  for (const CamHost& c : h->cams)
+    if (c.active && c.model != MCC_MODEL_EQUIDISTANT && c.model != MCC_MODEL_RADTAN) return fail(h, MCC_ERR_BAD_MODEL, "unknown distortion model: %d", c.model);
+  if (!h->params_valid || (long long)h->params.size() != mcc_num_params(h)) init_params(h);
+  if (h->structure_dirty) ST(build_structure(h));
+  ST(upload_obs(h));
+  ST(upload_params(h));
+  return MCC_OK;
+}
+
+// ---- kernel sequences ---------------------------------------------------------------------------
+mcc_status launch_setup(mcc_handle* h, int which) {
+  if (h->ngroups == 0) return MCC_OK;
+  k_group_setup<<<(h->ngroups + 127) / 128, 128, 0, h->stream>>>(h->ngroups, h->ncam(), h->d_cams.p, h->d_camp[which].p, h->d_pose[which].p, h->d_setup.p);
+  h->launches++;
+  CU(cudaGetLastError());
+  return MCC_OK;
+}
+
+// K5 at parameter set `which`: per-frame costs into cost_f_out; optional raw residuals
+mcc_status launch_cost(mcc_handle* h, int which, int use_loss, double* cost_f_out, double* res_out) {
+  ST(launch_setup(h, which));
+  if (h->ntiles) {
+    k_tile_cost<<<(h->ntiles + K1_WARPS - 1) / K1_WARPS, K1_WARPS * 32, 0, h->stream>>>(
+        h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p,
+        h->d_mask.p, h->d_tile_s.p, res_out);
+    h->launches++;
+    CU(cudaGetLastError());
+  }
+  if (h->nslots && cost_f_out) {
+    k_frame_cost<<<(h->nslots + 127) / 128, 128, 0, h->stream>>>(h->nslots, h->ncam(), h->d_gto.p, h->d_tile_s.p, use_loss, cost_f_out);
+    h->launches++;
+    CU(cudaGetLastError());
+  }
+  return MCC_OK;
+}
+
+mcc_status allreduce(mcc_handle* h, double* p, size_t n, int op) {
+  if (h->nranks <= 1 || n == 0) return MCC_OK;
+  NC(nccl().AllReduce(p, p, n, ncclFloat64_, op, h->comm, h->stream));
+  return MCC_OK;
+}
+
+// K1 at the current parameters: blocks, cost, gradient norm, |x|^2 -> d_scal[0..2], [8..9]
+mcc_status launch_jacobian(mcc_handle* h, int use_loss) {
+  const int which = h->cur;
+  ST(launch_setup(h, which));
+  if (h->ntiles) {
+    const size_t smem = (size_t)K1_WARPS * (64 * h->rowstride + 64) * sizeof(double);
+    k_tile_normal<<<(h->ntiles + K1_WARPS - 1) / K1_WARPS, K1_WARPS * 32, smem, h->stream>>>(
+        h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p,
+        h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p, h->rowstride);
+    h->launches++;
+    CU(cudaGetLastError());
+  }
+  k_frame_assemble<<<h->asm_grid, 128, std::max(h->E, 1) * sizeof(double), h->stream>>>(
+      h->nslots, h->ncam(), h->C, h->E, h->d_gto.p, h->d_cams.p, h->d_lut.p, h->d_cc.p, h->d_colmap.p, h->d_G.p, h->gstride, h->d_tile_s.p,
+      h->d_pose[which].p, use_loss, h->d_Hff.p, h->d_gf.p, h->d_Hfc.p, h->d_cost_f.p, h->d_gmax_f.p, h->d_xn2_f.p, h->d_cc_part.p);
+  h->launches++;
+  CU(cudaGetLastError());
+  if (h->E) {
+    k_reduce_rows<<<(h->E + 127) / 128, 128, 0, h->stream>>>(h->asm_grid, h->E, h->d_cc_part.p, h->d_cc_sum.p);
+    h->launches++;
+    CU(cudaGetLastError());
+  }
+  ReduceJobs jobs;
+  std::memset(&jobs, 0, sizeof(jobs));
+  jobs.j[0] = ReduceJob{h->d_cost_f.p, 0};
+  jobs.j[1] = ReduceJob{h->d_xn2_f.p, 0};
+  jobs.j[2] = ReduceJob{h->d_gmax_f.p, 1};
+  k_reduce_arrays<<<3, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p);
+  h->launches++;
+  CU(cudaGetLastError());
+  if (h->nranks > 1) {
+    NC(nccl().GroupStart());
+    ST(allreduce(h, h->d_cc_sum.p, h->E, ncclSum_));
+    ST(allreduce(h, h->d_scal.p, 2, ncclSum_));
+    ST(allreduce(h, h->d_scal.p + 2, 1, ncclMax_));
+    NC(nccl().GroupEnd());
+  }
+  k_scatter_cc<<<1, 1024, 0, h->stream>>>(h->C, h->E, h->d_cc.p, h->d_cc_sum.p, h->d_col_param.p, h->d_camp[which].p, h->d_Hcc.p, h->d_gc.p, h->d_scal.p + 8);
+  h->launches++;
+  CU(cudaGetLastError());
+  return MCC_OK;
+}
+
+mcc_status read_scalars(mcc_handle* h) {
+  CU(cudaMemcpyAsync(h->h_scal, h->d_scal.p, 32 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaMemcpyAsync(h->h_fail, h->d_fail.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  h->d2h += 32 * sizeof(double) + sizeof(int);
+  return MCC_OK;
+}
+
+// K2..K5 for one trust-region radius: candidate parameters in the other buffer, scalars in d_scal[3..6], [10..12]
+mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius) {
+  const int cur = h->cur, cand = 1 - cur;
+  const int C = h->C;
+  CU(cudaMemsetAsync(h->d_fail.p, 0, sizeof(int), h->stream));
+  {
+    const size_t smem = ((size_t)SY_FB * 6 * h->LD + SY_FB * 36 + SY_FB * 6) * sizeof(double);
+    dim3 grid(h->sy_gx, h->sy_gy);
+    k_schur_syrk<<<grid, SY_THREADS, smem, h->stream>>>(h->nslots, C, h->LD, h->npairs, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hff.p,
+                                                        h->d_gf.p, h->d_Hfc.p, h->d_scale_f.p, h->d_scale_c.p, h->d_Lf.p, h->d_S_part.p, h->d_fail.p);
+    h->launches++;
+    CU(cudaGetLastError());
+    const int n = h->npairs * SY_T * SY_T;
+    k_reduce_rows<<<(n + 127) / 128, 128, 0, h->stream>>>(h->sy_gx, n, h->d_S_part.p, h->d_S_sum.p);
+    h->launches++;
+    CU(cudaGetLastError());
+    ST(allreduce(h, h->d_S_sum.p, n, ncclSum_));
+  }
+  {
+    const size_t need = (size_t)(C + 1) * std::max(C, 1) * sizeof(double);
+    const int in_smem = need <= 200 * 1024;
+    k_solve_cam<<<1, 1024, in_smem ? need : 0, h->stream>>>(C, in_smem, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc.p, h->d_gc.p, h->d_S_sum.p,
+                                                           h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
+                                                           h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, h->d_fail.p);
+    h->launches++;
+    CU(cudaGetLastError());
+  }
+  if (h->nslots) {
+    k_backsub<<<(h->nslots + 3) / 4, 128, 0, h->stream>>>(h->nslots, C, h->d_Hff.p, h->d_gf.p, h->d_Hfc.p, h->d_Lf.p, h->d_scale_f.p, h->d_ysc.p,
+                                                         h->d_pose[cur].p, h->d_pose[cand].p, h->d_mcc_f.p, h->d_dx2_f.p, h->d_xn2c_f.p, h->d_fail.p);
+    h->launches++;
+    CU(cudaGetLastError());
+  }
+  ST(launch_cost(h, cand, o.use_loss, h->d_newcost_f.p, nullptr));
+  ReduceJobs jobs;
+  std::memset(&jobs, 0, sizeof(jobs));
+  jobs.j[0] = ReduceJob{h->d_newcost_f.p, 0};
+  jobs.j[1] = ReduceJob{h->d_mcc_f.p, 0};
+  jobs.j[2] = ReduceJob{h->d_dx2_f.p, 0};
+  jobs.j[3] = ReduceJob{h->d_xn2c_f.p, 0};
+  k_reduce_arrays<<<4, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p + 3);
+  h->launches++;
+  CU(cudaGetLastError());
+  if (h->nranks > 1) {
+    NC(nccl().GroupStart());
+    ST(allreduce(h, h->d_scal.p + 3, 4, ncclSum_));
+    NC(nccl().AllReduce(h->d_fail.p, h->d_fail.p, 1, ncclInt32_, ncclMax_, h->comm, h->stream));
+    NC(nccl().GroupEnd());
+  }
+  return MCC_OK;
+}
+
+// the LM loop
+mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
+  const double t_start = now_s();
+  double t_iter = t_start;
+  auto log_row = [&](double cost, double cc, double gm, double sn, double ratio, double radius) {
+    const double t = now_s();
+    if (S.trace_len < MCC_MAX_TRACE) {
+      const int i = S.trace_len++;
+      S.tr_cost[i] = cost; S.tr_cost_change[i] = cc; S.tr_gradient_max[i] = gm; S.tr_step_norm[i] = sn; S.tr_ratio[i] = ratio; S.tr_radius[i] = radius;
+      S.tr_iter_time[i] = t - t_iter;
+    }
+    if (o.verbose) {
+      if (S.num_iterations == 0) std::printf("iter      cost      cost_change  |gradient|   |step|    tr_ratio  tr_radius  ls_iter  iter_time  total_time\n");
+      std::printf("%4d  %.6e    %.2e    %.2e   %.2e   %.2e  %.2e        %d    %.2e    %.2e\n", S.num_iterations, cost, cc, gm, sn, ratio, radius,
+                  S.num_iterations ? 1 : 0, t - t_iter, t - t_start);
+    }
+    t_iter = t;
+    S.num_iterations++;
+  };
+  double t0 = now_s();
+  ST(launch_jacobian(h, o.use_loss));
+  ST(read_scalars(h));
+  S.t_jacobian += now_s() - t0; S.n_jacobian_evals++;
+  double cost = h->h_scal[0];
+  double x_norm = std::sqrt(h->h_scal[1] + h->h_scal[9]);
+  double gmax = std::max(h->h_scal[2], h->h_scal[8]);
+  S.initial_cost = cost;
+  k_jacobi_scale<<<(std::max(h->C, h->nslots * 6) + 127) / 128, 128, 0, h->stream>>>(h->nslots, h->C, o.jacobi_scaling, h->d_Hcc.p, h->d_Hff.p, h->d_scale_c.p, h->d_scale_f.p);
+  h->launches++;
+  CU(cudaGetLastError());
+  double radius = o.initial_trust_region_radius, decrease_factor = 2.0;
+  log_row(cost, 0, gmax, 0, 0, radius);
+  S.num_successful = 1;
+  auto finish = [&](int term, int why, double val) {
+    S.termination = term; S.why = why; S.why_value = val; S.final_cost = cost;
+    return MCC_OK;
+  };
+  if (gmax <= o.gradient_tolerance) return finish(0, 0, gmax);
+  int invalid_run = 0, iter = 0;
+  while (true) {
+    if (iter >= o.max_num_iterations) return finish(1, 3, iter);
+    iter++;
+    t0 = now_s();
+    ST(launch_step(h, o, radius));
+    ST(read_scalars(h));
+    const double dt = now_s() - t0;
+    S.t_linear += dt; S.n_linear_solves++; S.n_residual_evals++;
+    const int flags = *h->h_fail;
+    const double new_cost = h->h_scal[3];
+    const double mcc = h->h_scal[4] + h->h_scal[10];
+    const double step_norm = std::sqrt(h->h_scal[5] + h->h_scal[11]);
+    const double xn_cand = std::sqrt(h->h_scal[6] + h->h_scal[12]);
+    bool step_valid = flags == 0 && std::isfinite(mcc) && mcc > 0.0;
+    if (!step_valid) {
+      invalid_run++;
+      if (invalid_run >= o.max_num_consecutive_invalid_steps) return finish(2, 4, invalid_run);
+      radius /= decrease_factor; decrease_factor *= 2.0;
+      S.num_unsuccessful++;
+      log_row(cost, 0, gmax, 0, 0, radius);
+      if (radius < o.min_trust_region_radius) return finish(0, 5, radius);
+      continue;
+    }
+    invalid_run = 0;
+    if (step_norm <= o.parameter_tolerance * (x_norm + o.parameter_tolerance)) return finish(0, 1, step_norm / (x_norm + o.parameter_tolerance));
+    const double cost_change = cost - new_cost;
+    if (std::fabs(cost_change) <= o.function_tolerance * cost) return finish(0, 2, std::fabs(cost_change) / cost);
+    const double ratio = cost_change / mcc;
+    if (ratio > o.min_relative_decrease) {
+      h->cur = 1 - h->cur;
+      x_norm = xn_cand;
+      radius = radius / std::max(1.0 / 3.0, 1.0 - std::pow(2.0 * ratio - 1.0, 3));
+      radius = std::min(o.max_trust_region_radius, radius);
+      decrease_factor = 2.0;
+      t0 = now_s();
+      ST(launch_jacobian(h, o.use_loss));
+      ST(read_scalars(h));
+      S.t_jacobian += now_s() - t0; S.n_jacobian_evals++;
+      cost = h->h_scal[0];
+      gmax = std::max(h->h_scal[2], h->h_scal[8]);
+      S.num_successful++;
+      log_row(cost, cost_change, gmax, step_norm, ratio, radius);
+      if (gmax <= o.gradient_tolerance) return finish(0, 0, gmax);
+    } else {
+      radius /= decrease_factor; decrease_factor *= 2.0;
+      S.num_unsuccessful++;
+      log_row(cost, cost_change, 0.0, step_norm, ratio, radius);
+    }
+    if (radius < o.min_trust_region_radius) return finish(0, 5, radius);
+  }
+}
+
+}  // namespace
+
+// =================================================================================================
+// C ABI
+// =================================================================================================
+extern "C" {
+
+const char* mcc_version(void) { return "multicam_calibration_b200 0.1 (sm_100a, fp64)"; }
+
+void mcc_default_options(mcc_options* o) {
+  o->max_num_iterations = 200;          // calibrator.cpp:302
+  o->function_tolerance = 1e-12;        // calibrator.cpp:304
+  o->parameter_tolerance = 1e-12;       // calibrator.cpp:305
+  o->gradient_tolerance = 1e-10;
+  o->initial_trust_region_radius = 1e4;
+  o->max_trust_region_radius = 1e16;
+  o->min_trust_region_radius = 1e-32;
+  o->min_relative_decrease = 1e-3;
+  o->min_lm_diagonal = 1e-6;
+  o->max_lm_diagonal = 1e32;
+  o->max_num_consecutive_invalid_steps = 5;
+  o->jacobi_scaling = 1;
+  o->use_loss = 1;
+  o->verbose = 0;
+  o->keep_params = 0;
+}
+int mcc_summary_size(void) { return (int)sizeof(mcc_summary); }
+
+mcc_status mcc_create(mcc_handle** out) {
+  if (!out) return MCC_ERR_BAD_ARG;
+  *out = new (std::nothrow) mcc_handle();
+  return *out ? MCC_OK : MCC_ERR_BAD_ARG;
+}
+
+void mcc_destroy(mcc_handle* h) {
+  if (!h) return;
+  if (h->device >= 0) cudaSetDevice(h->device);
+  if (h->comm && nccl().CommDestroy) nccl().CommDestroy(h->comm);
+  DBuf<double>* dd[] = {&h->d_aos_w, &h->d_aos_i, &h->d_X, &h->d_Y, &h->d_Z, &h->d_U, &h->d_V, &h->d_res, &h->d_camp[0], &h->d_camp[1], &h->d_pose[0], &h->d_pose[1],
+                        &h->d_setup, &h->d_G, &h->d_tile_s, &h->d_Hff, &h->d_gf, &h->d_Hfc, &h->d_Lf, &h->d_cost_f, &h->d_gmax_f, &h->d_xn2_f, &h->d_newcost_f,
+                        &h->d_mcc_f, &h->d_dx2_f, &h->d_xn2c_f, &h->d_cc_part, &h->d_cc_sum, &h->d_Hcc, &h->d_gc, &h->d_scale_c, &h->d_scale_f, &h->d_S_part,
+                        &h->d_S_sum, &h->d_M, &h->d_yc, &h->d_ysc, &h->d_scal};
+  for (auto* b : dd) b->release();
+  h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_lut.release(); h->d_col_param.release(); h->d_fail.release();
+  h->d_cams.release(); h->d_cc.release(); h->d_colmap.release();
+  h->world.release(); h->image.release();
+  if (h->h_scal) cudaFreeHost(h->h_scal);
+  if (h->h_fail) cudaFreeHost(h->h_fail);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+const char* mcc_last_error(const mcc_handle* h) { return h ? h->err.c_str() : "null handle"; }
+
+mcc_status mcc_set_device(mcc_handle* h, int device) {
+  if (!h) return MCC_ERR_BAD_ARG;
+  if (h->stream) return fail(h, MCC_ERR_BAD_ARG, "device already in use by this handle");
+  h->device = device;
+  return MCC_OK;
+}
+
+mcc_status mcc_set_cameras(mcc_handle* h, int ncam, const mcc_camera* cams) {
+  if (!h || ncam < 0 || ncam > MCC_MAX_CAMERAS || (ncam && !cams)) return fail(h, MCC_ERR_BAD_ARG, "bad camera array");
+  if (h->nframes && ncam != h->ncam()) return fail(h, MCC_ERR_BAD_ARG, "camera count changed while frames are held");
+  std::vector<CamHost> v(ncam);
+  for (int k = 0; k < ncam; k++) {
+    const mcc_camera& c = cams[k];
+    if (c.n_intr != 4) return fail(h, MCC_ERR_BAD_ARG, "camera %d: n_intr must be 4", k);
+    if (c.n_dist < 0 || c.n_dist > MCC_MAX_DIST) return fail(h, MCC_ERR_BAD_ARG, "camera %d: n_dist must be 0..%d", k, MCC_MAX_DIST);
+    if (c.model != MCC_MODEL_EQUIDISTANT && c.model != MCC_MODEL_RADTAN) return fail(h, MCC_ERR_BAD_MODEL, "unknown distortion model: %d", c.model);
+    CamHost& d = v[k];
+    d.model = c.model; d.n_intr = 4; d.n_dist = c.n_dist;
+    for (int i = 0; i < 4; i++) d.intr[i] = c.intr[i];
+    for (int i = 0; i < c.n_dist; i++) d.dist[i] = c.dist[i];
+    std::memcpy(d.T, c.T_cn_cnm1, sizeof(d.T));
+    d.fix_intr = c.fix_intr; d.fix_extr = c.fix_extr; d.active = c.active;
+  }
+  h->cams.swap(v);
+  h->structure_dirty = true;
+  h->params_valid = false;
+  return MCC_OK;
+}
+
+mcc_status mcc_set_fix_all_intrinsics(mcc_handle* h, int fix) {
+  if (!h) return MCC_ERR_BAD_ARG;
+  h->fix_all = fix != 0;
+  h->structure_dirty = true;
+  return MCC_OK;
+}
+
+mcc_status mcc_set_camera_flags(mcc_handle* h, int cam, int fix_intr, int fix_extr, int active) {
+  if (!h || cam < 0 || cam >= h->ncam()) return fail(h, MCC_ERR_BAD_ARG, "bad camera index");
+  h->cams[cam].fix_intr = fix_intr; h->cams[cam].fix_extr = fix_extr; h->cams[cam].active = active;
+  h->structure_dirty = true;
+  return MCC_OK;
+}
+
+mcc_status mcc_add_frames(mcc_handle* h, int nframes, int ncam, const int* npts, const double* world_xyz, const double* image_uv, const double* poses) {
+  if (!h) return MCC_ERR_BAD_ARG;
+  if (ncam != h->ncam() || ncam == 0) {
+    std::fprintf(stderr, "number of cams != width of array!\n");   // calibrator.cpp:238
+    return fail(h, MCC_ERR_BAD_ARG, "number of cams != width of array!");
+  }
+  if (nframes < 0 || !npts || !poses) return fail(h, MCC_ERR_BAD_ARG, "null argument");
+  size_t n = 0;
+  for (size_t i = 0; i < (size_t)nframes * ncam; i++) { if (npts[i] < 0) return fail(h, MCC_ERR_BAD_ARG, "negative point count"); n += npts[i]; }
+  if (n && (!world_xyz || !image_uv)) return fail(h, MCC_ERR_BAD_ARG, "null point arrays");
+  if (!h->world.reserve(3 * (h->nobs + n), 3 * h->nobs) || !h->image.reserve(2 * (h->nobs + n), 2 * h->nobs)) return fail(h, MCC_ERR_BAD_ARG, "out of host memory");
+  parallel_memcpy(h->world.p + 3 * h->nobs, world_xyz, 3 * n * sizeof(double));
+  parallel_memcpy(h->image.p + 2 * h->nobs, image_uv, 2 * n * sizeof(double));
+  h->npts.insert(h->npts.end(), npts, npts + (size_t)nframes * ncam);
+  h->poses.insert(h->poses.end(), poses, poses + 16 * (size_t)nframes);
+  h->mask.resize(h->nobs + n, 1);
+  h->nobs += n;
+  h->nframes += nframes;
+  h->structure_dirty = h->obs_dirty = h->mask_dirty = true;
+  h->params_valid = false;
+  return MCC_OK;
+}
+
+mcc_status mcc_add_frame(mcc_handle* h, int ncam, const int* npts, const double* const* world_xyz, const double* const* image_uv, const double* T_c0_w) {
+  if (!h) return MCC_ERR_BAD_ARG;
+  if (ncam != h->ncam() || ncam == 0) {
+    std::fprintf(stderr, "number of cams != width of array!\n");
+    return fail(h, MCC_ERR_BAD_ARG, "number of cams != width of array!");
+  }
+  if (!npts || !T_c0_w) return fail(h, MCC_ERR_BAD_ARG, "null argument");
+  std::vector<double> w, im;
+  for (int k = 0; k < ncam; k++) {
+    if (npts[k] < 0 || (npts[k] && (!world_xyz || !image_uv || !world_xyz[k] || !image_uv[k]))) return fail(h, MCC_ERR_BAD_ARG, "bad point arrays");
+    if (npts[k]) { w.insert(w.end(), world_xyz[k], world_xyz[k] + 3 * (size_t)npts[k]); im.insert(im.end(), image_uv[k], image_uv[k] + 2 * (size_t)npts[k]); }
+  }
+  return mcc_add_frames(h, 1, ncam, npts, w.data(), im.data(), T_c0_w);
+}
+
+mcc_status mcc_clear_frames(mcc_handle* h) {
+  if (!h) return MCC_ERR_BAD_ARG;
+  h->npts.clear(); h->poses.clear(); h->mask.clear();
+  h->nobs = 0; h->nframes = 0;
+  h->structure_dirty = h->obs_dirty = h->mask_dirty = true;
+  h->params_valid = false;
+  return MCC_OK;
+}
+
+long long mcc_num_frames(const mcc_handle* h) { return h ? h->nframes : 0; }
+long long mcc_num_observations(const mcc_handle* h) { return h ? (long long)h->nobs : 0; }
+
+long long mcc_num_params(const mcc_handle* h) {
+  if (!h) return 0;
+  long long n = 0;
+  for (const CamHost& c : h->cams) n += c.nparam();
+  n += 6 * std::max(0, h->ncam() - 1);
+  return n + 6ll * h->nframes;
+}
+
+mcc_status mcc_init_params(mcc_handle* h) {
+  if (!h) return MCC_ERR_BAD_ARG;
+  init_params(h);
+  return MCC_OK;
+}
+
+mcc_status mcc_get_params(const mcc_handle* h, double* out, size_t n) {
+  if (!h || !out) return MCC_ERR_BAD_ARG;
+  if (!h->params_valid) return fail(const_cast<mcc_handle*>(h), MCC_ERR_NO_DATA, "parameters not initialised");
+  if (n < h->params.size()) return fail(const_cast<mcc_handle*>(h), MCC_ERR_BAD_ARG, "output too small: need %zu", h->params.size());
+  std::memcpy(out, h->params.data(), h->params.size() * sizeof(double));
+  return MCC_OK;
+}
+
+mcc_status mcc_set_params(mcc_handle* h, const double* in, size_t n) {
+  if (!h || !in) return MCC_ERR_BAD_ARG;
+  if ((long long)n != mcc_num_params(h)) return fail(h, MCC_ERR_BAD_ARG, "expected %lld parameters, got %zu", mcc_num_params(h), n);
+  h->params.assign(in, in + n);
+  h->params_valid = true;
+  h->params_dirty = true;
+  return MCC_OK;
+}
+
+mcc_status mcc_upload(mcc_handle* h) {
+  if (!h) return MCC_ERR_BAD_ARG;
+  ST(prepare(h));
+  CU(cudaStreamSynchronize(h->stream));
+  return MCC_OK;
+}
+
+mcc_status mcc_run(mcc_handle* h, const mcc_options* opts, mcc_summary* out) {
+  if (!h) return MCC_ERR_BAD_ARG;
+  mcc_options o;
+  mcc_default_options(&o);
+  if (opts) o = *opts;
+  mcc_summary local;
+  mcc_summary& S = out ? *out : local;
+  std::memset(&S, 0, sizeof(S));
+  if (h->cams.empty() || h->nframes == 0) {
+    std::fprintf(stderr, "no data to run on!\n");   // calibrator.cpp:287
+    S.termination = 2; S.why = 7;
+    return fail(h, MCC_ERR_NO_DATA, "no data to run on!");
+  }
+  const double t0 = now_s();
+  const long long l0 = h->launches, u0 = h->h2d, d0 = h->d2h;
+  if (!o.keep_params) init_params(h);
+  ST(prepare(h));
+  S.t_upload = now_s() - t0;
+  S.num_params = (int)h->params.size();
+  S.num_reduced_params = h->C + 6 * h->nslots;
+  S.num_residuals = h->nres;
+  if (o.verbose) std::printf("Num params: %d\nNum residuals: %lld\n", S.num_params, S.num_residuals);
+  if (h->nslots == 0 && h->nranks <= 1) { S.termination = 2; S.why = 7; return fail(h, MCC_ERR_NO_DATA, "no valid points in any active camera"); }
+  mcc_status st = solve(h, o, S);
+  if (st != MCC_OK) return st;
+  ST(download_params(h));
+  S.t_total = now_s() - t0;
+  S.n_kernel_launches = h->launches - l0;
+  S.h2d_bytes = h->h2d - u0;
+  S.d2h_bytes = h->d2h - d0;
+  return MCC_OK;
+}
+
+mcc_status mcc_get_camera(const mcc_handle* hc, int k, double* intr, double* dist, double* T_cn_cnm1) {
+  mcc_handle* h = const_cast<mcc_handle*>(hc);
+  if (!h || k < 0 || k >= h->ncam()) return fail(h, MCC_ERR_BAD_ARG, "bad camera index");
+  if (!h->params_valid) return fail(h, MCC_ERR_NO_DATA, "parameters not initialised");
+  int off = 0, num_intr = 0;
+  for (int i = 0; i < h->ncam(); i++) { if (i < k) off += h->cams[i].nparam(); num_intr += h->cams[i].nparam(); }
+  const CamHost& c = h->cams[k];
+  if (intr) for (int i = 0; i < 4; i++) intr[i] = h->params[off + i];
+  if (dist) for (int i = 0; i < c.n_dist; i++) dist[i] = h->params[off + 4 + i];
+  if (T_cn_cnm1) {
+    double Tk[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1}, Tp[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+    if (k > 0) {
+      h_rvec_tvec_to_transform(&h->params[num_intr + 6 * (k - 1)], Tk);
+      if (k > 1) h_rvec_tvec_to_transform(&h->params[num_intr + 6 * (k - 2)], Tp);
+      double inv[16];
+      h_mat4_inv(Tp, inv);
+      h_mat4_mul(Tk, inv, T_cn_cnm1);       // calibrator.cpp:441
+    } else {
+      std::memcpy(T_cn_cnm1, c.T, sizeof(Tk));
+    }
+  }
+  return MCC_OK;
+}
+
+long long mcc_num_residuals(const mcc_handle* hc) {
+  mcc_handle* h = const_cast<mcc_handle*>(hc);
+  if (!h) return 0;
+  long long n = 0;
+  size_t o = 0;
+  for (int f = 0; f < h->nframes; f++)
+    for (int k = 0; k < h->ncam(); k++) {
+      const int np = h->npts[(size_t)f * h->ncam() + k];
+      if (h->cams[k].active) for (int i = 0; i < np; i++) n += h->mask[o + i] != 0;
+      o += np;
+    }
+  return 2 * n;
+}
+
+mcc_status mcc_eval_residuals(mcc_handle* h, double* out_xy, size_t n_out) {
+  if (!h || !out_xy) return MCC_ERR_BAD_ARG;
+  ST(prepare(h));
+  if ((long long)n_out < h->nres) return fail(h, MCC_ERR_BAD_ARG, "output too small: need %lld doubles", h->nres);
+  CU(h->d_res.reserve(2 * std::max<size_t>(h->nobs, 1)));
+  ST(launch_cost(h, h->cur, 0, nullptr, h->d_res.p));
+  std::vector<double> all(2 * h->nobs);
+  CU(cudaMemcpyAsync(all.data(), h->d_res.p, all.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  h->d2h += all.size() * sizeof(double);
+  // compact: frames with residual blocks -> active cameras -> valid points (calibrator.cpp:336-347)
+  size_t w = 0;
+  const int ncam = h->ncam();
+  for (int s = 0; s < h->nslots; s++) {
+    const int f = h->slot_frame[s];
+    for (int k = 0; k < ncam; k++) {
+      if (!h->cams[k].active) continue;
+      const size_t o0 = h->group_obs0[(size_t)f * ncam + k];
+      const int np = h->npts[(size_t)f * ncam + k];
+      for (int i = 0; i < np; i++)
+        if (h->mask[o0 + i]) { out_xy[w++] = all[2 * (o0 + i)]; out_xy[w++] = all[2 * (o0 + i) + 1]; }
+    }
+  }
+  return MCC_OK;
+}
+
+mcc_status mcc_eval_cost(mcc_handle* h, int use_loss, double* cost) {
+  if (!h || !cost) return MCC_ERR_BAD_ARG;
+  ST(prepare(h));
+  ST(launch_cost(h, h->cur, use_loss, h->d_newcost_f.p, nullptr));
+  ReduceJobs jobs;
+  std::memset(&jobs, 0, sizeof(jobs));
+  jobs.j[0] = ReduceJob{h->d_newcost_f.p, 0};
+  k_reduce_arrays<<<1, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p + 3);
+  h->launches++;
+  CU(cudaGetLastError());
+  ST(allreduce(h, h->d_scal.p + 3, 1, ncclSum_));
+  ST(read_scalars(h));
+  *cost = h->h_scal[3];
+  return MCC_OK;
+}
+
+mcc_status mcc_remove_outliers(mcc_handle* h, double max_err, long long* ndropped) {
+  if (!h) return MCC_ERR_BAD_ARG;
+  ST(prepare(h));
+  CU(h->d_res.reserve(2 * std::max<size_t>(h->nobs, 1)));
+  ST(launch_cost(h, h->cur, 0, nullptr, h->d_res.p));
+  std::vector<double> all(2 * h->nobs);
+  CU(cudaMemcpyAsync(all.data(), h->d_res.p, all.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  h->d2h += all.size() * sizeof(double);
+  const double m2 = max_err * max_err;
+  long long dropped = 0;
+  const int ncam = h->ncam();
+  for (int s = 0; s < h->nslots; s++) {
+    const int f = h->slot_frame[s];
+    for (int k = 0; k < ncam; k++) {
+      if (!h->cams[k].active) continue;
+      const size_t o0 = h->group_obs0[(size_t)f * ncam + k];
+      const int np = h->npts[(size_t)f * ncam + k];
+      for (int i = 0; i < np; i++) {
+        if (!h->mask[o0 + i]) continue;
+        const double dx = all[2 * (o0 + i)], dy = all[2 * (o0 + i) + 1];
+        if (dx * dx + dy * dy > m2) { h->mask[o0 + i] = 0; dropped++; }
+      }
+    }
+  }
+  if (dropped) { h->mask_dirty = true; h->structure_dirty = true; }
+  if (ndropped) *ndropped = dropped;
+  return MCC_OK;
+}
+
+mcc_status mcc_get_mask(const mcc_handle* h, uint8_t* out, size_t n) {
+  if (!h || !out || n < h->nobs) return MCC_ERR_BAD_ARG;
+  std::memcpy(out, h->mask.data(), h->nobs);
+  return MCC_OK;
+}
+mcc_status mcc_set_mask(mcc_handle* h, const uint8_t* in, size_t n) {
+  if (!h || !in || n != h->nobs) return MCC_ERR_BAD_ARG;
+  std::memcpy(h->mask.data(), in, n);
+  h->mask_dirty = true; h->structure_dirty = true;
+  return MCC_OK;
+}
+
+int mcc_num_reduced_cam_cols(const mcc_handle* hc) {
+  mcc_handle* h = const_cast<mcc_handle*>(hc);
+  if (!h) return 0;
+  int C = 0;
+  for (int k = 0; k < h->ncam(); k++) if (!(h->fix_all || h->cams[k].fix_intr)) C += h->cams[k].nparam();
+  for (int k = 1; k < h->ncam(); k++) if (!h->cams[k].fix_extr) C += 6;
+  return C;
+}
+long long mcc_num_active_frames(const mcc_handle* h) { return h ? h->nslots : 0; }
+
+mcc_status mcc_eval_normal_blocks(mcc_handle* h, int use_loss, double* cost, double* Hcc, double* gc, double* Hff, double* gf, double* Hfc, int* frame_ids) {
+  if (!h) return MCC_ERR_BAD_ARG;
+  ST(prepare(h));
+  ST(launch_jacobian(h, use_loss));
+  ST(read_scalars(h));
+  if (cost) *cost = h->h_scal[0];
+  const size_t C = h->C, ns = h->nslots;
+  if (Hcc && C) CU(cudaMemcpyAsync(Hcc, h->d_Hcc.p, C * C * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  if (gc && C) CU(cudaMemcpyAsync(gc, h->d_gc.p, C * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  if (Hff && ns) CU(cudaMemcpyAsync(Hff, h->d_Hff.p, ns * 36 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  if (gf && ns) CU(cudaMemcpyAsync(gf, h->d_gf.p, ns * 6 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  if (Hfc && ns && C) CU(cudaMemcpyAsync(Hfc, h->d_Hfc.p, ns * 6 * C * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  if (frame_ids) for (size_t s = 0; s < ns; s++) frame_ids[s] = h->slot_frame[s];
+  return MCC_OK;
+}
+
+mcc_status mcc_comm_unique_id(unsigned char id[MCC_UNIQUE_ID_BYTES]) {
+  if (!id || !nccl().ok()) return MCC_ERR_NCCL;
+  ncclUniqueId u;
+  if (nccl().GetUniqueId(&u) != 0) return MCC_ERR_NCCL;
+  std::memcpy(id, u.internal, MCC_UNIQUE_ID_BYTES);
+  return MCC_OK;
+}
+
+mcc_status mcc_comm_init(mcc_handle* h, int nranks, int rank, const unsigned char id[MCC_UNIQUE_ID_BYTES]) {
+  if (!h || !id || nranks < 1 || rank < 0 || rank >= nranks) return fail(h, MCC_ERR_BAD_ARG, "bad communicator arguments");
+  if (nranks == 1) { h->nranks = 1; h->rank = 0; return MCC_OK; }
+  if (!nccl().ok()) return fail(h, MCC_ERR_NCCL, "libnccl.so.2 not found");
+  ST(ensure_device(h));
+  ncclUniqueId u;
+  std::memcpy(u.internal, id, MCC_UNIQUE_ID_BYTES);
+  NC(nccl().CommInitRank(&h->comm, nranks, u, rank));
+  h->nranks = nranks; h->rank = rank;
+  return MCC_OK;
+}
+
+void mcc_transform_to_rvec_tvec(const double T[16], double out6[6]) { h_transform_to_rvec_tvec(T, out6); }
+void mcc_rvec_tvec_to_transform(const double in6[6], double T[16]) { h_rvec_tvec_to_transform(in6, T); }
+
+}  // extern "C"

@@ -1,0 +1,258 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU oracle on the same inputs.
+
+Tolerances (BASELINE.json north_star): final cost <= 1e-9 relative, parameters <= 1e-7 relative, same LM
+iteration count.  Unit-level tolerances are stated in each test.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b, floor=1e-300):
+    return np.max(np.abs(np.asarray(a) - np.asarray(b))) / max(np.max(np.abs(np.asarray(b))), floor)
+
+
+def _param_rel(pg, po):
+    # relative per parameter, with an absolute floor for parameters that are ~0 (tangential coefficients, angles)
+    return np.max(np.abs(pg - po) / np.maximum(np.abs(po), 1e-3))
+
+
+def _pair(rig):
+    from multicam_calibration_b200 import capi
+    import oracle
+    cal = capi.calibrator_from_rig(rig, device=0)
+    cal.initParams()
+    return cal, oracle.Oracle(rig)
+
+
+def test_residuals_match_oracle(small_rig):
+    """testCalibration (calibrator.cpp:316-351): raw residuals, same order, |diff| <= 1e-10 px"""
+    cal, orc = _pair(small_rig)
+    rg = cal.testCalibration().reshape(-1)
+    ro = orc.residuals()
+    assert rg.shape == ro.shape
+    assert np.max(np.abs(rg - ro)) <= 1e-10
+    cal.close()
+
+
+@pytest.mark.parametrize("use_loss", [True, False])
+def test_normal_blocks_match_oracle(small_rig, use_loss):
+    """K1: analytic Jacobian blocks vs the oracle's Jet autodiff blocks; relative to each block's max, <= 1e-10"""
+    cal, orc = _pair(small_rig)
+    g = cal.normalBlocks(use_loss)
+    o = orc.normal_blocks(use_loss)
+    assert abs(g["cost"] - o["cost"]) <= 1e-12 * o["cost"]
+    assert list(g["frames"]) == list(o["frames"])
+    for key in ("Hcc", "gc", "Hff", "gf", "Hfc"):
+        assert g[key].shape == o[key].shape, key
+        assert _rel(g[key], o[key]) <= 1e-10, (key, _rel(g[key], o[key]))
+    # per frame as well (small frames must not hide behind large ones)
+    for s in range(len(o["frames"])):
+        assert _rel(g["Hff"][s], o["Hff"][s]) <= 1e-10
+        assert _rel(g["Hfc"][s], o["Hfc"][s]) <= 1e-10
+    cal.close()
+
+
+def test_jacobian_guards(built):
+    """rotation vector below 1e-8 (utils.h:31-38: identity, zero derivative) and a point on the optical axis
+    (utils.h:69-72) -- blocks must match the oracle's Jets there too"""
+    from multicam_calibration_b200 import synth, capi
+    import oracle
+    rig = synth.make_synthetic_rig(2, 6, 3, detect_prob=1.0, noise_px=0.1, mixed_models=False)
+    # frame 0: zero rotation pose; camera 1 extrinsic rotation zero as well
+    rig.poses[0, :3, :3] = np.eye(3)
+    rig.cameras[1].T_cn_cnm1[:3, :3] = np.eye(3)
+    # put the first world point of frame 0 / cam 0 exactly on the optical axis of cam0
+    off = rig.frame_offsets()
+    t = rig.poses[0, :3, 3]
+    rig.world[off[0], :] = [-t[0], -t[1], 0.0]
+    cal, orc = _pair(rig)
+    g, o = cal.normalBlocks(True), orc.normal_blocks(True)
+    for key in ("Hcc", "gc", "Hff", "gf", "Hfc"):
+        assert _rel(g[key], o[key]) <= 1e-10, key
+    # the rotation block of frame 0 and of the cam1 extrinsics must be exactly zero
+    assert np.all(g["Hff"][0][:3, :] == 0.0)
+    assert np.all(o["Hff"][0][:3, :] == 0.0)
+    cal.close()
+
+
+def _check_solve(cal, orc, opt_g=None, opt_o=None, same_iters=True):
+    from multicam_calibration_b200 import capi
+    sg = cal.runCalibration(opt_g)
+    so = orc.solve(opt_o)
+    assert abs(sg.initial_cost - so.initial_cost) <= 1e-9 * so.initial_cost
+    assert abs(sg.final_cost - so.final_cost) <= 1e-9 * so.final_cost, (sg.final_cost, so.final_cost)
+    pg, po = cal.getParams(), orc.get_params()
+    assert _param_rel(pg, po) <= 1e-7, _param_rel(pg, po)
+    if same_iters:
+        assert sg.num_iterations == so.num_iterations, (sg.num_iterations, so.num_iterations)
+        assert sg.why == so.why
+        assert sg.num_successful == so.num_successful and sg.num_unsuccessful == so.num_unsuccessful
+        tg, to = sg.trace(), so.trace()
+        # the radius depends continuously on tr_ratio = cost_change / model_cost_change, and cost_change of the last
+        # rows is a difference of nearly equal costs: compare loosely
+        np.testing.assert_allclose(tg["radius"], to["radius"], rtol=2e-3)
+        np.testing.assert_allclose(tg["cost"], to["cost"], rtol=1e-9)
+    return sg, so
+
+
+def test_solve_small_rig(small_rig):
+    cal, orc = _pair(small_rig)
+    _check_solve(cal, orc)
+    # getCalibrationResults (calibrator.cpp:415-463)
+    res = cal.getCalibrationResults()
+    for k in range(small_rig.num_cameras):
+        intr, dist, T = orc.get_camera(k)
+        np.testing.assert_allclose(res[k].intrinsics, intr, rtol=1e-7)
+        np.testing.assert_allclose(res[k].distortion_coeffs, dist, rtol=1e-7, atol=1e-10)
+        if k > 0:
+            np.testing.assert_allclose(res[k].T_cn_cnm1, T, rtol=1e-7, atol=1e-10)
+    cal.close()
+
+
+def test_solve_radtan_kat(kat_rigs):
+    """config c2: the reference's test/radtan fixture; must land on the reference's logged result
+    (/root/reference/test/radtan/correct_output.txt) exactly like the oracle does"""
+    import json, os
+    from conftest import GOLDEN
+    ref = json.load(open(os.path.join(GOLDEN, "reference_logs.json")))["radtan"]
+    cal, orc = _pair(kat_rigs["radtan"])
+    sg, so = _check_solve(cal, orc)
+    assert sg.num_residuals == ref["num_residuals"] and sg.num_params == ref["num_params"]
+    assert sg.num_iterations == ref["iterations"] == 12
+    assert sg.why == 1  # parameter tolerance
+    assert abs(sg.final_cost - ref["final_cost"]) <= 5e-7 * ref["final_cost"]   # printed to 7 digits
+    res = cal.getCalibrationResults()[0]
+    for got, want in zip(res.distortion_coeffs, ref["distortion_coeffs"]):
+        assert abs(got - want) <= 5.1e-6 * abs(want) + 1e-12   # printed to 6 significant digits
+    cal.close()
+
+
+def test_solve_equidistant_kat(kat_rigs):
+    """config c1: test/equidistant.  The tail of this solve sits at the rounding floor (|cost change|/cost ~1e-11),
+    so the iteration count is compared within +-2 and the results at full tolerance."""
+    import json, os
+    from conftest import GOLDEN
+    ref = json.load(open(os.path.join(GOLDEN, "reference_logs.json")))["equidistant"]
+    cal, orc = _pair(kat_rigs["equidistant"])
+    sg, so = _check_solve(cal, orc, same_iters=False)
+    assert abs(sg.num_iterations - so.num_iterations) <= 2
+    assert abs(sg.final_cost - ref["final_cost"]) <= 5e-7 * ref["final_cost"]
+    res = cal.getCalibrationResults()[0]
+    for got, want in zip(res.distortion_coeffs, ref["distortion_coeffs"]):
+        assert abs(got - want) <= 5.1e-6 * abs(want) + 1e-12
+    r = cal.testCalibration()
+    assert abs(np.hypot(r[:, 0], r[:, 1]).max() - ref["max_reproj_err"]) <= 1e-9
+    cal.close()
+
+
+def test_solve_c3_stereo(c3_rig):
+    """config c3: README-scale stereo rig, 409 frames, ~202k residuals, 2476 params"""
+    cal, orc = _pair(c3_rig)
+    sg, so = _check_solve(cal, orc)
+    assert sg.num_params == 2476
+    cal.close()
+
+
+@pytest.mark.parametrize("flags", [
+    dict(fix_all=True),                                     # node-level fix_intrinsics
+    dict(fix_intr=[1, 0, 0]),                               # one camera's intrinsics fixed
+    dict(fix_extr=[0, 1, 0]),                               # one extrinsic block fixed
+    dict(active=[1, 0, 1]),                                 # example_calib_manager.py: a camera switched off
+    dict(fix_intr=[1, 1, 1], fix_extr=[0, 1, 1]),           # extrinsics-only stage
+])
+def test_fix_and_active_flags(small_rig, flags):
+    """the fix / active matrix of example_calib_manager.py:22-52 and calibrator.cpp:510-521"""
+    from multicam_calibration_b200 import capi
+    from multicam_calibration_b200.rig import Rig
+    import oracle
+    cams = [c.copy() for c in small_rig.cameras]
+    for k, c in enumerate(cams):
+        c.fix_intrinsics = bool(flags.get("fix_intr", [0, 0, 0])[k])
+        c.fix_extrinsics = bool(flags.get("fix_extr", [0, 0, 0])[k])
+        c.active = bool(flags.get("active", [1, 1, 1])[k])
+    rig = Rig(cams, small_rig.npts, small_rig.world, small_rig.image, small_rig.poses, fix_all_intrinsics=flags.get("fix_all", False))
+    cal, orc = _pair(rig)
+    sg, so = _check_solve(cal, orc)
+    assert sg.num_reduced_params == so.num_reduced_params
+    assert sg.num_residuals == so.num_residuals
+    cal.close()
+
+
+def test_remove_outliers_then_resolve(small_rig):
+    """calibrate() with outlier_pixel_threshold (calibration_nodelet.cpp:202-207): solve, drop, solve again"""
+    from multicam_calibration_b200.rig import Rig
+    rig = Rig([c.copy() for c in small_rig.cameras], small_rig.npts, small_rig.world, small_rig.image.copy(), small_rig.poses)
+    rng = np.random.default_rng(5)
+    bad = rng.choice(rig.num_obs, 25, replace=False)
+    rig.image[bad] += rng.uniform(8, 20, (25, 2))
+    cal, orc = _pair(rig)
+    _check_solve(cal, orc)
+    ng, no = cal.removeOutliers(3.0), orc.remove_outliers(3.0)
+    assert ng == no and ng >= 20
+    assert np.array_equal(cal.getMask(), orc.get_mask())
+    orc.init_params()          # runCalibration restarts from the initial values (calibrator.cpp:293-294)
+    _check_solve(cal, orc)
+    cal.close()
+
+
+def test_empty_and_ragged_frames(built):
+    """frames where some / all cameras saw nothing (calibrator.cpp:482-485: no residual block, pose untouched)"""
+    from multicam_calibration_b200 import synth
+    from multicam_calibration_b200.rig import Rig
+    base = synth.make_synthetic_rig(3, 16, 21, detect_prob=0.7)
+    off = base.frame_offsets()
+    keep = np.ones(base.num_obs, dtype=bool)
+    npts = base.npts.copy()
+    # frame 2: nothing at all; frame 5: only camera 1; frame 7: camera 0 missing
+    def drop(f, k):
+        o = off[f] + npts[f, :k].sum()
+        keep[o:o + npts[f, k]] = False
+    for f, ks in ((2, (0, 1, 2)), (5, (0, 2)), (7, (0,))):
+        for k in ks:
+            drop(f, k)
+    for f, ks in ((2, (0, 1, 2)), (5, (0, 2)), (7, (0,))):
+        for k in ks:
+            npts[f, k] = 0
+    rig = Rig(base.cameras, npts, base.world[keep], base.image[keep], base.poses)
+    cal, orc = _pair(rig)
+    p0 = cal.getParams().copy()
+    _check_solve(cal, orc)
+    pg = cal.getParams()
+    C = rig.num_cam_params
+    assert np.array_equal(pg[C + 12:C + 18], p0[C + 12:C + 18])   # pose of the empty frame is untouched
+    cal.close()
+
+
+def test_add_points_one_by_one_equals_bulk(small_rig):
+    """Calibrator::addPoints frame by frame == the bulk entry point"""
+    from multicam_calibration_b200 import capi
+    rig = small_rig
+    cal = capi.Calibrator(0)
+    cal.setCameras(rig.cameras)
+    off = rig.frame_offsets()
+    for f in range(rig.num_frames):
+        wp, ip, o = [], [], off[f]
+        for k in range(rig.num_cameras):
+            n = rig.npts[f, k]
+            wp.append(rig.world[o:o + n]); ip.append(rig.image[o:o + n]); o += n
+        cal.addPoints(f, wp, ip, rig.poses[f])
+    bulk = capi.calibrator_from_rig(rig, 0)
+    s1, s2 = cal.runCalibration(), bulk.runCalibration()
+    assert s1.final_cost == s2.final_cost and s1.num_iterations == s2.num_iterations   # bit-reproducible
+    assert np.array_equal(cal.getParams(), bulk.getParams())
+    cal.close(); bulk.close()
+
+
+def test_error_conventions(small_rig):
+    from multicam_calibration_b200 import capi
+    cal = capi.Calibrator(0)
+    with pytest.raises(capi.MccError) as e:
+        cal.runCalibration()                       # "no data to run on!" (calibrator.cpp:286-289)
+    assert e.value.status == -1
+    cal.setCameras(small_rig.cameras)
+    with pytest.raises(capi.MccError) as e:
+        cal.addPoints(0, [np.zeros((0, 3))], [np.zeros((0, 2))], np.eye(4))   # camera-count mismatch (calibrator.cpp:236-240)
+    assert e.value.status == -2
+    cal.close()
