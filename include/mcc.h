@@ -172,6 +172,20 @@ mcc_status mcc_eval_normal_blocks(mcc_handle* h, int use_loss, double* cost, dou
 mcc_status mcc_comm_unique_id(unsigned char id[MCC_UNIQUE_ID_BYTES]);
 mcc_status mcc_comm_init(mcc_handle* h, int nranks, int rank, const unsigned char id[MCC_UNIQUE_ID_BYTES]);
 
+/* Measurement hooks for bench.py (no reference counterpart: Ceres only prints wall-clock phase times,
+ * calibrator.cpp:312).  mcc_timer_start/stop bracket a region with CUDA events on the handle's stream (the
+ * stream every kernel of this library is launched on).  With kernel timing enabled every launch is bracketed
+ * by an event pair and accumulated per kernel class; mcc_get_kernel_times returns ms and launch counts for
+ * mcc_num_kernel_classes() classes named by mcc_kernel_class_name().  mcc_measure_fp64_peak times a
+ * dependent-chain DFMA kernel: the measured FP64 roofline denominator of this GPU. */
+mcc_status mcc_timer_start(mcc_handle* h);
+mcc_status mcc_timer_stop(mcc_handle* h, double* ms);
+mcc_status mcc_set_kernel_timing(mcc_handle* h, int enabled);
+int mcc_num_kernel_classes(void);
+const char* mcc_kernel_class_name(int c);
+mcc_status mcc_get_kernel_times(mcc_handle* h, double* ms, long long* counts, int n);
+mcc_status mcc_measure_fp64_peak(int device, double* tflops);
+
 /* Transform helpers used by the facade: Eigen AngleAxisd(R) route of transform_to_rvec_tvec
  * (calibrator.cpp:157-170) and utils::rotation_matrix (utils.h:29-39). */
 void mcc_transform_to_rvec_tvec(const double T[16], double out6[6]);

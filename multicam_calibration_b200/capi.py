@@ -70,7 +70,8 @@ SYMBOLS = ["mcc_version", "mcc_default_options", "mcc_summary_size", "mcc_create
            "mcc_num_frames", "mcc_num_observations", "mcc_init_params", "mcc_num_params", "mcc_get_params", "mcc_set_params", "mcc_upload",
            "mcc_run", "mcc_get_camera", "mcc_num_residuals", "mcc_eval_residuals", "mcc_eval_cost", "mcc_remove_outliers", "mcc_get_mask",
            "mcc_set_mask", "mcc_num_reduced_cam_cols", "mcc_num_active_frames", "mcc_eval_normal_blocks", "mcc_comm_unique_id", "mcc_comm_init",
-           "mcc_transform_to_rvec_tvec", "mcc_rvec_tvec_to_transform"]
+           "mcc_transform_to_rvec_tvec", "mcc_rvec_tvec_to_transform", "mcc_timer_start", "mcc_timer_stop", "mcc_set_kernel_timing",
+           "mcc_num_kernel_classes", "mcc_kernel_class_name", "mcc_get_kernel_times", "mcc_measure_fp64_peak"]
 
 
 def build(force: bool = False) -> str:
@@ -131,6 +132,13 @@ def lib():
     L.mcc_transform_to_rvec_tvec.restype = None
     L.mcc_rvec_tvec_to_transform.argtypes = [dp, dp]
     L.mcc_rvec_tvec_to_transform.restype = None
+    L.mcc_timer_start.argtypes = [vp]
+    L.mcc_timer_stop.argtypes = [vp, dp]
+    L.mcc_set_kernel_timing.argtypes = [vp, C.c_int]
+    L.mcc_kernel_class_name.argtypes = [C.c_int]
+    L.mcc_kernel_class_name.restype = C.c_char_p
+    L.mcc_get_kernel_times.argtypes = [vp, dp, C.POINTER(C.c_longlong), C.c_int]
+    L.mcc_measure_fp64_peak.argtypes = [C.c_int, dp]
     assert L.mcc_summary_size() == C.sizeof(Summary), (L.mcc_summary_size(), C.sizeof(Summary))
     _lib = L
     return L
@@ -156,6 +164,15 @@ def comm_unique_id() -> bytes:
     if st != 0:
         raise MccError(st, "ncclGetUniqueId failed (libnccl.so.2 not loadable?)")
     return bytes(buf)
+
+
+def measure_fp64_peak(device: int = 0) -> float:
+    """measured FP64 FMA throughput of the device in TFLOP/s"""
+    t = C.c_double()
+    st = lib().mcc_measure_fp64_peak(int(device), C.byref(t))
+    if st != 0:
+        raise MccError(st, "mcc_measure_fp64_peak failed")
+    return t.value
 
 
 def transform_to_rvec_tvec(T) -> np.ndarray:
@@ -327,6 +344,25 @@ class Calibrator:
         Hff = np.zeros((max(ns, 1), 6, 6)); gf = np.zeros((max(ns, 1), 6)); Hfc = np.zeros((max(ns, 1), 6, max(Cc, 1))); ids = np.zeros(max(ns, 1), dtype=np.int32)
         self._check(self._L.mcc_eval_normal_blocks(self.h, int(use_loss), C.byref(cost), _dp(Hcc) if Cc else None, _dp(gc), _dp(Hff), _dp(gf), _dp(Hfc), _ip(ids)))
         return dict(cost=cost.value, Hcc=Hcc, gc=gc[:Cc], Hff=Hff[:ns], gf=gf[:ns], Hfc=Hfc.reshape(-1)[:ns * 6 * Cc].reshape(ns, 6, Cc), frames=ids[:ns])
+
+    def timerStart(self):
+        self._check(self._L.mcc_timer_start(self.h))
+
+    def timerStop(self) -> float:
+        """milliseconds between timerStart and now, by CUDA events on the library's stream"""
+        ms = C.c_double()
+        self._check(self._L.mcc_timer_stop(self.h, C.byref(ms)))
+        return ms.value
+
+    def setKernelTiming(self, enabled: bool):
+        self._check(self._L.mcc_set_kernel_timing(self.h, int(enabled)))
+
+    def kernelTimes(self) -> dict:
+        n = self._L.mcc_num_kernel_classes()
+        ms = np.zeros(n)
+        cnt = np.zeros(n, dtype=np.int64)
+        self._check(self._L.mcc_get_kernel_times(self.h, _dp(ms), cnt.ctypes.data_as(C.POINTER(C.c_longlong)), n))
+        return {self._L.mcc_kernel_class_name(i).decode(): dict(ms=float(ms[i]), launches=int(cnt[i])) for i in range(n)}
 
     def commInit(self, nranks: int, rank: int, unique_id: bytes):
         buf = (C.c_ubyte * UNIQUE_ID_BYTES).from_buffer_copy(unique_id)

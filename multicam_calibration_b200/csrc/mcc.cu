@@ -203,6 +203,21 @@ void parallel_memcpy(void* dst, const void* src, size_t bytes) {
   for (auto& t : th) t.join();
 }
 
+// kernel categories for the optional per-launch CUDA-event timing (mcc_set_kernel_timing)
+enum { KC_SETUP = 0, KC_TILE_NORMAL, KC_ASSEMBLE, KC_SCHUR, KC_SOLVE, KC_BACKSUB, KC_TILE_COST, KC_REDUCE, KC_OTHER, KC_COUNT };
+struct KPending { cudaEvent_t a, b; int cat; };
+
+// FP64 FMA throughput probe: 8 independent dependent-chains per thread
+__global__ void k_dfma_peak(double* out, int iters) {
+  const double b = 1.0000000001, c = 1e-12;
+  double a0 = threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+  for (int i = 0; i < iters; i++) {
+    a0 = fma(a0, b, c); a1 = fma(a1, b, c); a2 = fma(a2, b, c); a3 = fma(a3, b, c);
+    a4 = fma(a4, b, c); a5 = fma(a5, b, c); a6 = fma(a6, b, c); a7 = fma(a7, b, c);
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+}
+
 // AoS -> SoA on the device (observations arrive as Point3 / Point2 arrays, types.h:17-47)
 __global__ void k_aos_to_soa(size_t n, const double* __restrict__ w, const double* __restrict__ im, double* __restrict__ X,
                              double* __restrict__ Y, double* __restrict__ Z, double* __restrict__ U, double* __restrict__ V) {
@@ -255,6 +270,13 @@ struct mcc_handle {
   int asm_grid = 0, sy_gx = 0, sy_gy = 0;
   bool attrs_set = false;
   long long launches = 0, h2d = 0, d2h = 0;
+  // optional per-launch timing
+  bool ktiming = false;
+  std::vector<cudaEvent_t> ev_pool;
+  std::vector<KPending> ev_pending;
+  double kc_ms[KC_COUNT] = {0};
+  long long kc_n[KC_COUNT] = {0};
+  cudaEvent_t tm_a = nullptr, tm_b = nullptr;
 
   // ---- comm
   ncclComm_t comm = nullptr;
@@ -289,6 +311,37 @@ mcc_status fail(mcc_handle* h, mcc_status st, const char* fmt, ...) {
     int r_ = (call);                                                                                                  \
     if (r_ != 0) return fail(h, MCC_ERR_NCCL, "%s failed: %s", #call, nccl().GetErrorString ? nccl().GetErrorString(r_) : "?"); \
   } while (0)
+
+struct KScope {
+  mcc_handle* h;
+  KPending p;
+  bool on;
+  KScope(mcc_handle* hh, int cat) : h(hh), on(hh->ktiming) {
+    h->launches++;
+    if (!on) return;
+    auto get = [&]() {
+      cudaEvent_t e = nullptr;
+      if (!h->ev_pool.empty()) { e = h->ev_pool.back(); h->ev_pool.pop_back(); }
+      else cudaEventCreate(&e);
+      return e;
+    };
+    p.a = get(); p.b = get(); p.cat = cat;
+    cudaEventRecord(p.a, h->stream);
+  }
+  ~KScope() {
+    if (!on) return;
+    cudaEventRecord(p.b, h->stream);
+    h->ev_pending.push_back(p);
+  }
+};
+void resolve_ktiming(mcc_handle* h) {   // call after a stream synchronize
+  for (KPending& p : h->ev_pending) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) { h->kc_ms[p.cat] += ms; h->kc_n[p.cat]++; }
+    h->ev_pool.push_back(p.a); h->ev_pool.push_back(p.b);
+  }
+  h->ev_pending.clear();
+}
 
 mcc_status ensure_device(mcc_handle* h) {
   int n = 0;
@@ -516,8 +569,10 @@ mcc_status upload_obs(mcc_handle* h) {
       CU(cudaMemcpyAsync(h->d_aos_w.p, h->world.p, 3 * n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
       CU(cudaMemcpyAsync(h->d_aos_i.p, h->image.p, 2 * n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
       h->h2d += 5 * n * sizeof(double);
-      k_aos_to_soa<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(n, h->d_aos_w.p, h->d_aos_i.p, h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p);
-      h->launches++;
+      {
+        KScope ks(h, KC_OTHER);
+        k_aos_to_soa<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(n, h->d_aos_w.p, h->d_aos_i.p, h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p);
+      }
       CU(cudaGetLastError());
     }
     h->obs_dirty = false;
@@ -568,8 +623,10 @@ mcc_status prepare(mcc_handle* h) {
 // ---- kernel sequences ---------------------------------------------------------------------------
 mcc_status launch_setup(mcc_handle* h, int which) {
   if (h->ngroups == 0) return MCC_OK;
-  k_group_setup<<<(h->ngroups + 127) / 128, 128, 0, h->stream>>>(h->ngroups, h->ncam(), h->d_cams.p, h->d_camp[which].p, h->d_pose[which].p, h->d_setup.p);
-  h->launches++;
+  {
+    KScope ks(h, KC_SETUP);
+    k_group_setup<<<(h->ngroups + 127) / 128, 128, 0, h->stream>>>(h->ngroups, h->ncam(), h->d_cams.p, h->d_camp[which].p, h->d_pose[which].p, h->d_setup.p);
+  }
   CU(cudaGetLastError());
   return MCC_OK;
 }
@@ -578,15 +635,19 @@ mcc_status launch_setup(mcc_handle* h, int which) {
 mcc_status launch_cost(mcc_handle* h, int which, int use_loss, double* cost_f_out, double* res_out) {
   ST(launch_setup(h, which));
   if (h->ntiles) {
-    k_tile_cost<<<(h->ntiles + K1_WARPS - 1) / K1_WARPS, K1_WARPS * 32, 0, h->stream>>>(
+    {
+      KScope ks(h, KC_TILE_COST);
+      k_tile_cost<<<(h->ntiles + K1_WARPS - 1) / K1_WARPS, K1_WARPS * 32, 0, h->stream>>>(
         h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p,
         h->d_mask.p, h->d_tile_s.p, res_out);
-    h->launches++;
+    }
     CU(cudaGetLastError());
   }
   if (h->nslots && cost_f_out) {
-    k_frame_cost<<<(h->nslots + 127) / 128, 128, 0, h->stream>>>(h->nslots, h->ncam(), h->d_gto.p, h->d_tile_s.p, use_loss, cost_f_out);
-    h->launches++;
+    {
+      KScope ks(h, KC_REDUCE);
+      k_frame_cost<<<(h->nslots + 127) / 128, 128, 0, h->stream>>>(h->nslots, h->ncam(), h->d_gto.p, h->d_tile_s.p, use_loss, cost_f_out);
+    }
     CU(cudaGetLastError());
   }
   return MCC_OK;
@@ -604,20 +665,26 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss) {
   ST(launch_setup(h, which));
   if (h->ntiles) {
     const size_t smem = (size_t)K1_WARPS * (64 * h->rowstride + 64) * sizeof(double);
-    k_tile_normal<<<(h->ntiles + K1_WARPS - 1) / K1_WARPS, K1_WARPS * 32, smem, h->stream>>>(
+    {
+      KScope ks(h, KC_TILE_NORMAL);
+      k_tile_normal<<<(h->ntiles + K1_WARPS - 1) / K1_WARPS, K1_WARPS * 32, smem, h->stream>>>(
         h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p,
         h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p, h->rowstride);
-    h->launches++;
+    }
     CU(cudaGetLastError());
   }
-  k_frame_assemble<<<h->asm_grid, 128, std::max(h->E, 1) * sizeof(double), h->stream>>>(
+  {
+    KScope ks(h, KC_ASSEMBLE);
+    k_frame_assemble<<<h->asm_grid, 128, std::max(h->E, 1) * sizeof(double), h->stream>>>(
       h->nslots, h->ncam(), h->C, h->E, h->d_gto.p, h->d_cams.p, h->d_lut.p, h->d_cc.p, h->d_colmap.p, h->d_G.p, h->gstride, h->d_tile_s.p,
       h->d_pose[which].p, use_loss, h->d_Hff.p, h->d_gf.p, h->d_Hfc.p, h->d_cost_f.p, h->d_gmax_f.p, h->d_xn2_f.p, h->d_cc_part.p);
-  h->launches++;
+  }
   CU(cudaGetLastError());
   if (h->E) {
-    k_reduce_rows<<<(h->E + 127) / 128, 128, 0, h->stream>>>(h->asm_grid, h->E, h->d_cc_part.p, h->d_cc_sum.p);
-    h->launches++;
+    {
+      KScope ks(h, KC_REDUCE);
+      k_reduce_rows<<<(h->E + 127) / 128, 128, 0, h->stream>>>(h->asm_grid, h->E, h->d_cc_part.p, h->d_cc_sum.p);
+    }
     CU(cudaGetLastError());
   }
   ReduceJobs jobs;
@@ -625,8 +692,10 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss) {
   jobs.j[0] = ReduceJob{h->d_cost_f.p, 0};
   jobs.j[1] = ReduceJob{h->d_xn2_f.p, 0};
   jobs.j[2] = ReduceJob{h->d_gmax_f.p, 1};
-  k_reduce_arrays<<<3, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p);
-  h->launches++;
+  {
+    KScope ks(h, KC_REDUCE);
+    k_reduce_arrays<<<3, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p);
+  }
   CU(cudaGetLastError());
   if (h->nranks > 1) {
     NC(nccl().GroupStart());
@@ -635,8 +704,10 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss) {
     ST(allreduce(h, h->d_scal.p + 2, 1, ncclMax_));
     NC(nccl().GroupEnd());
   }
-  k_scatter_cc<<<1, 1024, 0, h->stream>>>(h->C, h->E, h->d_cc.p, h->d_cc_sum.p, h->d_col_param.p, h->d_camp[which].p, h->d_Hcc.p, h->d_gc.p, h->d_scal.p + 8);
-  h->launches++;
+  {
+    KScope ks(h, KC_REDUCE);
+    k_scatter_cc<<<1, 1024, 0, h->stream>>>(h->C, h->E, h->d_cc.p, h->d_cc_sum.p, h->d_col_param.p, h->d_camp[which].p, h->d_Hcc.p, h->d_gc.p, h->d_scal.p + 8);
+  }
   CU(cudaGetLastError());
   return MCC_OK;
 }
@@ -646,6 +717,7 @@ mcc_status read_scalars(mcc_handle* h) {
   CU(cudaMemcpyAsync(h->h_fail, h->d_fail.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaStreamSynchronize(h->stream));
   h->d2h += 32 * sizeof(double) + sizeof(int);
+  if (h->ktiming) resolve_ktiming(h);
   return MCC_OK;
 }
 
@@ -657,29 +729,37 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius) {
   {
     const size_t smem = ((size_t)SY_FB * 6 * h->LD + SY_FB * 36 + SY_FB * 6) * sizeof(double);
     dim3 grid(h->sy_gx, h->sy_gy);
-    k_schur_syrk<<<grid, SY_THREADS, smem, h->stream>>>(h->nslots, C, h->LD, h->npairs, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hff.p,
+    {
+      KScope ks(h, KC_SCHUR);
+      k_schur_syrk<<<grid, SY_THREADS, smem, h->stream>>>(h->nslots, C, h->LD, h->npairs, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hff.p,
                                                         h->d_gf.p, h->d_Hfc.p, h->d_scale_f.p, h->d_scale_c.p, h->d_Lf.p, h->d_S_part.p, h->d_fail.p);
-    h->launches++;
+    }
     CU(cudaGetLastError());
     const int n = h->npairs * SY_T * SY_T;
-    k_reduce_rows<<<(n + 127) / 128, 128, 0, h->stream>>>(h->sy_gx, n, h->d_S_part.p, h->d_S_sum.p);
-    h->launches++;
+    {
+      KScope ks(h, KC_REDUCE);
+      k_reduce_rows<<<(n + 127) / 128, 128, 0, h->stream>>>(h->sy_gx, n, h->d_S_part.p, h->d_S_sum.p);
+    }
     CU(cudaGetLastError());
     ST(allreduce(h, h->d_S_sum.p, n, ncclSum_));
   }
   {
     const size_t need = (size_t)(C + 1) * std::max(C, 1) * sizeof(double);
     const int in_smem = need <= 200 * 1024;
-    k_solve_cam<<<1, 1024, in_smem ? need : 0, h->stream>>>(C, in_smem, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc.p, h->d_gc.p, h->d_S_sum.p,
+    {
+      KScope ks(h, KC_SOLVE);
+      k_solve_cam<<<1, 1024, in_smem ? need : 0, h->stream>>>(C, in_smem, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc.p, h->d_gc.p, h->d_S_sum.p,
                                                            h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
                                                            h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, h->d_fail.p);
-    h->launches++;
+    }
     CU(cudaGetLastError());
   }
   if (h->nslots) {
-    k_backsub<<<(h->nslots + 3) / 4, 128, 0, h->stream>>>(h->nslots, C, h->d_Hff.p, h->d_gf.p, h->d_Hfc.p, h->d_Lf.p, h->d_scale_f.p, h->d_ysc.p,
+    {
+      KScope ks(h, KC_BACKSUB);
+      k_backsub<<<(h->nslots + 3) / 4, 128, 0, h->stream>>>(h->nslots, C, h->d_Hff.p, h->d_gf.p, h->d_Hfc.p, h->d_Lf.p, h->d_scale_f.p, h->d_ysc.p,
                                                          h->d_pose[cur].p, h->d_pose[cand].p, h->d_mcc_f.p, h->d_dx2_f.p, h->d_xn2c_f.p, h->d_fail.p);
-    h->launches++;
+    }
     CU(cudaGetLastError());
   }
   ST(launch_cost(h, cand, o.use_loss, h->d_newcost_f.p, nullptr));
@@ -689,8 +769,10 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius) {
   jobs.j[1] = ReduceJob{h->d_mcc_f.p, 0};
   jobs.j[2] = ReduceJob{h->d_dx2_f.p, 0};
   jobs.j[3] = ReduceJob{h->d_xn2c_f.p, 0};
-  k_reduce_arrays<<<4, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p + 3);
-  h->launches++;
+  {
+    KScope ks(h, KC_REDUCE);
+    k_reduce_arrays<<<4, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p + 3);
+  }
   CU(cudaGetLastError());
   if (h->nranks > 1) {
     NC(nccl().GroupStart());
@@ -728,8 +810,10 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
   double x_norm = std::sqrt(h->h_scal[1] + h->h_scal[9]);
   double gmax = std::max(h->h_scal[2], h->h_scal[8]);
   S.initial_cost = cost;
-  k_jacobi_scale<<<(std::max(h->C, h->nslots * 6) + 127) / 128, 128, 0, h->stream>>>(h->nslots, h->C, o.jacobi_scaling, h->d_Hcc.p, h->d_Hff.p, h->d_scale_c.p, h->d_scale_f.p);
-  h->launches++;
+  {
+    KScope ks(h, KC_OTHER);
+    k_jacobi_scale<<<(std::max(h->C, h->nslots * 6) + 127) / 128, 128, 0, h->stream>>>(h->nslots, h->C, o.jacobi_scaling, h->d_Hcc.p, h->d_Hff.p, h->d_scale_c.p, h->d_scale_f.p);
+  }
   CU(cudaGetLastError());
   double radius = o.initial_trust_region_radius, decrease_factor = 2.0;
   log_row(cost, 0, gmax, 0, 0, radius);
@@ -840,6 +924,9 @@ void mcc_destroy(mcc_handle* h) {
   h->world.release(); h->image.release();
   if (h->h_scal) cudaFreeHost(h->h_scal);
   if (h->h_fail) cudaFreeHost(h->h_fail);
+  for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
+  for (KPending& pe : h->ev_pending) { cudaEventDestroy(pe.a); cudaEventDestroy(pe.b); }
+  if (h->tm_a) { cudaEventDestroy(h->tm_a); cudaEventDestroy(h->tm_b); }
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -1081,8 +1168,10 @@ mcc_status mcc_eval_cost(mcc_handle* h, int use_loss, double* cost) {
   ReduceJobs jobs;
   std::memset(&jobs, 0, sizeof(jobs));
   jobs.j[0] = ReduceJob{h->d_newcost_f.p, 0};
-  k_reduce_arrays<<<1, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p + 3);
-  h->launches++;
+  {
+    KScope ks(h, KC_REDUCE);
+    k_reduce_arrays<<<1, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p + 3);
+  }
   CU(cudaGetLastError());
   ST(allreduce(h, h->d_scal.p + 3, 1, ncclSum_));
   ST(read_scalars(h));
@@ -1176,6 +1265,74 @@ mcc_status mcc_comm_init(mcc_handle* h, int nranks, int rank, const unsigned cha
   std::memcpy(u.internal, id, MCC_UNIQUE_ID_BYTES);
   NC(nccl().CommInitRank(&h->comm, nranks, u, rank));
   h->nranks = nranks; h->rank = rank;
+  return MCC_OK;
+}
+
+mcc_status mcc_set_kernel_timing(mcc_handle* h, int enabled) {
+  if (!h) return MCC_ERR_BAD_ARG;
+  h->ktiming = enabled != 0;
+  for (int i = 0; i < KC_COUNT; i++) { h->kc_ms[i] = 0.0; h->kc_n[i] = 0; }
+  return MCC_OK;
+}
+
+int mcc_num_kernel_classes(void) { return KC_COUNT; }
+const char* mcc_kernel_class_name(int c) {
+  static const char* names[KC_COUNT] = {"group_setup", "tile_normal", "frame_assemble", "schur_syrk", "solve_cam", "backsub", "tile_cost", "reduce", "other"};
+  return (c >= 0 && c < KC_COUNT) ? names[c] : "";
+}
+
+mcc_status mcc_get_kernel_times(mcc_handle* h, double* ms, long long* counts, int n) {
+  if (!h || n < KC_COUNT) return MCC_ERR_BAD_ARG;
+  if (h->stream) { CU(cudaStreamSynchronize(h->stream)); resolve_ktiming(h); }
+  for (int i = 0; i < KC_COUNT; i++) { if (ms) ms[i] = h->kc_ms[i]; if (counts) counts[i] = h->kc_n[i]; }
+  return MCC_OK;
+}
+
+mcc_status mcc_timer_start(mcc_handle* h) {
+  if (!h) return MCC_ERR_BAD_ARG;
+  ST(ensure_device(h));
+  if (!h->tm_a) { CU(cudaEventCreate(&h->tm_a)); CU(cudaEventCreate(&h->tm_b)); }
+  CU(cudaStreamSynchronize(h->stream));
+  CU(cudaEventRecord(h->tm_a, h->stream));
+  return MCC_OK;
+}
+
+mcc_status mcc_timer_stop(mcc_handle* h, double* ms) {
+  if (!h || !ms || !h->tm_a) return MCC_ERR_BAD_ARG;
+  CU(cudaEventRecord(h->tm_b, h->stream));
+  CU(cudaEventSynchronize(h->tm_b));
+  float f = 0.f;
+  CU(cudaEventElapsedTime(&f, h->tm_a, h->tm_b));
+  *ms = f;
+  return MCC_OK;
+}
+
+mcc_status mcc_measure_fp64_peak(int device, double* tflops) {
+  mcc_handle* h = nullptr;
+  if (!tflops) return MCC_ERR_BAD_ARG;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { cudaGetLastError(); return MCC_ERR_NO_DEVICE; }
+  CU(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device));
+  const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 16;
+  double* out = nullptr;
+  CU(cudaMalloc((void**)&out, (size_t)blocks * threads * sizeof(double)));
+  cudaEvent_t a, b;
+  CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b));
+  double best = 0.0;
+  for (int rep = 0; rep < 4; rep++) {
+    CU(cudaEventRecord(a, 0));
+    k_dfma_peak<<<blocks, threads>>>(out, iters);
+    CU(cudaEventRecord(b, 0));
+    CU(cudaEventSynchronize(b));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, a, b));
+    const double tf = 2.0 * 8.0 * iters * (double)blocks * threads / (ms * 1e-3) / 1e12;
+    if (rep > 0) best = std::max(best, tf);
+  }
+  cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(out);
+  *tflops = best;
   return MCC_OK;
 }
 
