@@ -186,6 +186,32 @@ const char* mcc_kernel_class_name(int c);
 mcc_status mcc_get_kernel_times(mcc_handle* h, double* ms, long long* counts, int n);
 mcc_status mcc_measure_fp64_peak(int device, double* tflops);
 
+/* No counterpart in the reference.  Sum of squared reprojection residuals of n observations of ONE camera under
+ * ONE rigid transform -- the arithmetic of the residual-only pass (FrameResidual with T = double) -- for callers
+ * that cannot allocate device memory at the point of the call: a per-frame quality monitor inside a live image
+ * callback, where cudaMalloc's device-wide synchronisation and unbounded latency stall the other streams of the
+ * process, or a process whose device memory is already claimed up front by another allocator (a perception stack's
+ * arena, torch's caching allocator) so that a cudaMalloc can simply fail.  This call performs NO cudaMalloc /
+ * cudaFree and calls no allocating library routine; it needs no handle.
+ *   Inputs, all DEVICE pointers owned by the caller: d_intr = [fx, fy, cx, cy, dist[0..n_dist)], d_Rt = 12 doubles
+ *   (R row-major, then t; X_cam = R X_world + t, i.e. R = R_c R_f and t = R_c t_f + t_c of calibrator.cpp:124-125),
+ *   SoA observations d_X, d_Y, d_Z, d_U, d_V [n], d_mask [n] or NULL (all valid).
+ *   Output: d_sum_sq[0] = sum over valid points of |projection - (u,v)|^2 (device); cost without loss = half of it.
+ *   stream: a cudaStream_t (NULL = default stream); the call only enqueues two kernels and returns.
+ * Scratch: one partial sum per 128 observations in a file-scope `static __device__` array of
+ * MCC_NOALLOC_MAX_OBS / 128 doubles (256 KiB, held by every GPU that loads the library until the process exits).
+ * n > MCC_NOALLOC_MAX_OBS is rejected with MCC_ERR_TOO_LARGE (message in errbuf, which may be NULL).
+ * The FIRST call on each device looks up the array's device address (cudaGetSymbolAddress, that device current);
+ * make that first call outside any stream capture.  All calls on a device share the one array, which keeps the
+ * previous call's partial sums: every slot a call reads it has first overwritten itself, so nothing needs
+ * clearing, but two calls whose kernels overlap on the GPU (different streams, or several host threads) race on
+ * it -- serialise them on one stream. */
+#define MCC_NOALLOC_MAX_OBS 4194304
+mcc_status mcc_reprojection_cost_noalloc(int model, int n_dist, const double* d_intr, const double* d_Rt, size_t n,
+                                         const double* d_X, const double* d_Y, const double* d_Z, const double* d_U,
+                                         const double* d_V, const uint8_t* d_mask, double* d_sum_sq, void* stream,
+                                         char* errbuf, size_t errbuf_len);
+
 /* Transform helpers used by the facade: Eigen AngleAxisd(R) route of transform_to_rvec_tvec
  * (calibrator.cpp:157-170) and utils::rotation_matrix (utils.h:29-39). */
 void mcc_transform_to_rvec_tvec(const double T[16], double out6[6]);

@@ -71,7 +71,8 @@ SYMBOLS = ["mcc_version", "mcc_default_options", "mcc_summary_size", "mcc_create
            "mcc_run", "mcc_get_camera", "mcc_num_residuals", "mcc_eval_residuals", "mcc_eval_cost", "mcc_remove_outliers", "mcc_get_mask",
            "mcc_set_mask", "mcc_num_reduced_cam_cols", "mcc_num_active_frames", "mcc_eval_normal_blocks", "mcc_comm_unique_id", "mcc_comm_init",
            "mcc_transform_to_rvec_tvec", "mcc_rvec_tvec_to_transform", "mcc_timer_start", "mcc_timer_stop", "mcc_set_kernel_timing",
-           "mcc_num_kernel_classes", "mcc_kernel_class_name", "mcc_get_kernel_times", "mcc_measure_fp64_peak"]
+           "mcc_num_kernel_classes", "mcc_kernel_class_name", "mcc_get_kernel_times", "mcc_measure_fp64_peak",
+           "mcc_reprojection_cost_noalloc"]
 
 
 def build(force: bool = False) -> str:
@@ -139,6 +140,7 @@ def lib():
     L.mcc_kernel_class_name.restype = C.c_char_p
     L.mcc_get_kernel_times.argtypes = [vp, dp, C.POINTER(C.c_longlong), C.c_int]
     L.mcc_measure_fp64_peak.argtypes = [C.c_int, dp]
+    L.mcc_reprojection_cost_noalloc.argtypes = [C.c_int, C.c_int] + [vp, vp, C.c_size_t] + [vp] * 8 + [C.c_char_p, C.c_size_t]
     assert L.mcc_summary_size() == C.sizeof(Summary), (L.mcc_summary_size(), C.sizeof(Summary))
     _lib = L
     return L
@@ -173,6 +175,20 @@ def measure_fp64_peak(device: int = 0) -> float:
     if st != 0:
         raise MccError(st, "mcc_measure_fp64_peak failed")
     return t.value
+
+
+NOALLOC_MAX_OBS = 4194304
+
+
+def reprojection_cost_noalloc(model: int, n_dist: int, d_intr: int, d_Rt: int, n: int, d_X: int, d_Y: int, d_Z: int, d_U: int, d_V: int,
+                              d_mask: Optional[int], d_sum_sq: int, stream: int = 0) -> None:
+    """mcc_reprojection_cost_noalloc over raw DEVICE addresses (ints); raises MccError with the library's message.
+    The library allocates nothing in this call; the caller owns every buffer."""
+    err = C.create_string_buffer(512)
+    st = lib().mcc_reprojection_cost_noalloc(int(model), int(n_dist), d_intr, d_Rt, int(n), d_X, d_Y, d_Z, d_U, d_V, d_mask, d_sum_sq,
+                                             stream, err, len(err))
+    if st != 0:
+        raise MccError(st, err.value.decode())
 
 
 def transform_to_rvec_tvec(T) -> np.ndarray:

@@ -19,6 +19,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -1333,6 +1334,134 @@ mcc_status mcc_measure_fp64_peak(int device, double* tflops) {
   }
   cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(out);
   *tflops = best;
+  return MCC_OK;
+}
+
+// -------------------------------------------------------------------------------------------------
+// mcc_reprojection_cost_noalloc: the residual-only pass (k_tile_cost's arithmetic) for callers that must not
+// allocate device memory.  The per-tile partial sums that the handle-based path keeps in a cudaMalloc'ed buffer
+// live here in a fixed file-scope device array instead; its size bounds the number of observations per call.
+// -------------------------------------------------------------------------------------------------
+}  // extern "C"
+
+namespace {
+
+constexpr int NA_TILE = 128;                                          // observations per warp
+constexpr int NA_MAX_TILES = MCC_NOALLOC_MAX_OBS / NA_TILE;           // 32768 partial sums = 256 KiB per GPU
+static __device__ __align__(256) double g_noalloc_scratch[NA_MAX_TILES];
+
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol; the device address is looked up once per
+// device with cudaGetSymbolAddress and cached here.
+constexpr int NA_MAX_DEVICES = 64;
+double* g_noalloc_ptr[NA_MAX_DEVICES] = {nullptr};
+std::mutex g_noalloc_mu;
+
+__global__ void __launch_bounds__(K1_WARPS * 32)
+k_cost_static(size_t n, int model, int nd, const double* __restrict__ intr, const double* __restrict__ Rt,
+              const double* __restrict__ oX, const double* __restrict__ oY, const double* __restrict__ oZ,
+              const double* __restrict__ oU, const double* __restrict__ oV, const uint8_t* __restrict__ omask,
+              double* __restrict__ scratch) {
+  __shared__ double smem[K1_WARPS][32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const size_t tile = (size_t)blockIdx.x * K1_WARPS + warp;
+  const size_t o0 = tile * NA_TILE;
+  if (o0 >= n) return;
+  double* sS = smem[warp];
+  double* sI = sS + 12;
+  if (lane < 12) sS[lane] = Rt[lane];                       // R row-major (9) then t (3)
+  else if (lane < 16 + nd) sI[lane - 12] = intr[lane - 12];  // fx fy cx cy D...
+  __syncwarp();
+  const int count = (int)min((size_t)NA_TILE, n - o0);
+  double ssum = 0.0;
+  for (int base = 0; base < count; base += 32) {
+    const int idx = base + lane;
+    if (idx < count) {
+      const size_t o = o0 + idx;
+      if (!omask || omask[o]) {
+        const double X = oX[o], Y = oY[o], Z = oZ[o];
+        const double x = sS[0] * X + sS[1] * Y + sS[2] * Z + sS[9];
+        const double y = sS[3] * X + sS[4] * Y + sS[5] * Z + sS[10];
+        const double z = sS[6] * X + sS[7] * Y + sS[8] * Z + sS[11];
+        double u, v, d0, d1;
+        if (model == 0) project_equidistant<false>(x, y, z, sI, nd, u, v, nullptr, nullptr, d0, d1, nullptr, nullptr);
+        else project_radtan<false>(x, y, z, sI, nd, u, v, nullptr, nullptr, d0, d1, nullptr, nullptr);
+        const double ru = u - oU[o], rv = v - oV[o];
+        ssum += ru * ru + rv * rv;
+      }
+    }
+  }
+  ssum = warp_sum(ssum);
+  if (lane == 0) scratch[tile] = ssum;    // every slot in [0, ntiles) is overwritten: nothing has to start at zero
+}
+
+// out[0] = sum of scratch[0 .. ntiles) in a fixed order (one CTA); slots beyond ntiles keep older calls' values
+// and are never read
+__global__ void __launch_bounds__(1024)
+k_cost_static_reduce(int ntiles, const double* __restrict__ scratch, double* __restrict__ out) {
+  __shared__ double red[1024];
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int per = (ntiles + nt - 1) / nt;
+  const int i0 = tid * per, i1 = min(ntiles, i0 + per);
+  double a = 0.0;
+  for (int i = i0; i < i1; i++) a += scratch[i];
+  red[tid] = a;
+  __syncthreads();
+  for (int o = nt / 2; o > 0; o >>= 1) { if (tid < o) red[tid] += red[tid + o]; __syncthreads(); }
+  if (tid == 0) out[0] = red[0];
+}
+
+mcc_status na_fail(char* errbuf, size_t errbuf_len, mcc_status st, const char* fmt, ...) {
+  if (errbuf && errbuf_len) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(errbuf, errbuf_len, fmt, ap);
+    va_end(ap);
+  }
+  return st;
+}
+
+}  // namespace
+
+extern "C" {
+
+mcc_status mcc_reprojection_cost_noalloc(int model, int n_dist, const double* d_intr, const double* d_Rt, size_t n,
+                                         const double* d_X, const double* d_Y, const double* d_Z, const double* d_U,
+                                         const double* d_V, const uint8_t* d_mask, double* d_sum_sq, void* stream,
+                                         char* errbuf, size_t errbuf_len) {
+  if (errbuf && errbuf_len) errbuf[0] = 0;
+  if (model != MCC_MODEL_EQUIDISTANT && model != MCC_MODEL_RADTAN) return na_fail(errbuf, errbuf_len, MCC_ERR_BAD_MODEL, "unknown distortion model: %d", model);
+  if (n_dist < 0 || n_dist > MCC_MAX_DIST) return na_fail(errbuf, errbuf_len, MCC_ERR_BAD_ARG, "n_dist must be 0..%d, got %d", MCC_MAX_DIST, n_dist);
+  if (n > (size_t)MCC_NOALLOC_MAX_OBS)
+    return na_fail(errbuf, errbuf_len, MCC_ERR_TOO_LARGE,
+                   "%zu observations exceed MCC_NOALLOC_MAX_OBS = %d (the fixed device scratch holds one partial sum per %d observations); "
+                   "split the call or use mcc_eval_cost on a handle", n, MCC_NOALLOC_MAX_OBS, NA_TILE);
+  if (!d_intr || !d_Rt || !d_sum_sq || (n && (!d_X || !d_Y || !d_Z || !d_U || !d_V))) return na_fail(errbuf, errbuf_len, MCC_ERR_BAD_ARG, "null device pointer");
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { cudaGetLastError(); return na_fail(errbuf, errbuf_len, MCC_ERR_NO_DEVICE, "cudaGetDevice failed: %s (no CPU fallback)", cudaGetErrorString(e)); }
+  if (dev < 0 || dev >= NA_MAX_DEVICES) return na_fail(errbuf, errbuf_len, MCC_ERR_BAD_ARG, "device ordinal %d out of range", dev);
+  double* scratch = nullptr;
+  {
+    // once per device, with that device current: resolve the device address of the static array
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+      double* p = nullptr;
+      e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+      if (e != cudaSuccess || !p) { cudaGetLastError(); return na_fail(errbuf, errbuf_len, MCC_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch) failed: %s", cudaGetErrorString(e)); }
+      g_noalloc_ptr[dev] = p;
+    }
+    scratch = g_noalloc_ptr[dev];
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int ntiles = (int)((n + NA_TILE - 1) / NA_TILE);
+  if (ntiles) {
+    k_cost_static<<<(ntiles + K1_WARPS - 1) / K1_WARPS, K1_WARPS * 32, 0, st>>>(n, model, n_dist, d_intr, d_Rt, d_X, d_Y, d_Z, d_U, d_V, d_mask, scratch);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return na_fail(errbuf, errbuf_len, MCC_ERR_CUDA, "k_cost_static launch failed: %s", cudaGetErrorString(e));
+  }
+  k_cost_static_reduce<<<1, 1024, 0, st>>>(ntiles, scratch, d_sum_sq);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return na_fail(errbuf, errbuf_len, MCC_ERR_CUDA, "k_cost_static_reduce launch failed: %s", cudaGetErrorString(e));
   return MCC_OK;
 }
 
