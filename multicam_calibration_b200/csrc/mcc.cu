@@ -957,9 +957,13 @@ mcc_status mcc_set_cameras(mcc_handle* h, int ncam, const mcc_camera* cams) {
     std::memcpy(d.T, c.T_cn_cnm1, sizeof(d.T));
     d.fix_intr = c.fix_intr; d.fix_extr = c.fix_extr; d.active = c.active;
   }
+  // like the reference (calibrator.cpp:225-227) this replaces calibrationData_ only: params_ of a finished run
+  // stay valid for testCalibration / removeOutliers as long as the parameter layout is unchanged
+  bool same_layout = v.size() == h->cams.size();
+  for (size_t k = 0; same_layout && k < v.size(); k++) same_layout = v[k].n_dist == h->cams[k].n_dist;
   h->cams.swap(v);
   h->structure_dirty = true;
-  h->params_valid = false;
+  if (!same_layout) h->params_valid = false;
   return MCC_OK;
 }
 
