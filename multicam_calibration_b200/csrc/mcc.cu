@@ -357,7 +357,9 @@ mcc_status ensure_device(mcc_handle* h) {
   if (!h->h_scal) CU(cudaHostAlloc((void**)&h->h_scal, 32 * sizeof(double), cudaHostAllocDefault));
   if (!h->h_fail) CU(cudaHostAlloc((void**)&h->h_fail, sizeof(int), cudaHostAllocDefault));
   if (!h->attrs_set) {
-    CU(cudaFuncSetAttribute(k_tile_normal, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(k_tile_normal<15>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_tile_normal<21>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU(cudaFuncSetAttribute(k_tile_normal<27>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_schur_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(k_solve_cam, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(k_frame_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
@@ -445,8 +447,7 @@ mcc_status build_structure(mcc_handle* h) {
     if (c.active) { max_nb = std::max(max_nb, m.nb); max_nblk = std::max(max_nblk, m.nblk); }
   }
   h->gstride = 9 * max_nblk;
-  h->rowstride = 3 * max_nb;
-  if (h->rowstride % 2 == 0) h->rowstride++;
+  h->rowstride = max_nb <= 5 ? 15 : (max_nb <= 7 ? 21 : 27);   // the instantiations of k_tile_normal<RS>
 
   // reduced column -> (camera, local column)
   std::vector<int2> colmap(std::max(C, 1));
@@ -666,12 +667,15 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss) {
   ST(launch_setup(h, which));
   if (h->ntiles) {
     const size_t smem = (size_t)K1_WARPS * (64 * h->rowstride + 64) * sizeof(double);
-    {
-      KScope ks(h, KC_TILE_NORMAL);
-      k_tile_normal<<<(h->ntiles + K1_WARPS - 1) / K1_WARPS, K1_WARPS * 32, smem, h->stream>>>(
-        h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p,
-        h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p, h->rowstride);
-    }
+    const int grid = (h->ntiles + K1_WARPS - 1) / K1_WARPS;
+    KScope ks(h, KC_TILE_NORMAL);
+#define MCC_LAUNCH_TILE_NORMAL(RS)                                                                                                          \
+    k_tile_normal<RS><<<grid, K1_WARPS * 32, smem, h->stream>>>(h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, \
+                                                                 h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p, h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p)
+    if (h->rowstride == 15) MCC_LAUNCH_TILE_NORMAL(15);
+    else if (h->rowstride == 21) MCC_LAUNCH_TILE_NORMAL(21);
+    else MCC_LAUNCH_TILE_NORMAL(27);
+#undef MCC_LAUNCH_TILE_NORMAL
     CU(cudaGetLastError());
   }
   {
