@@ -361,7 +361,7 @@ mcc_status ensure_device(mcc_handle* h) {
     CU(cudaFuncSetAttribute(k_tile_normal<21>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_tile_normal<27>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_schur_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    CU(cudaFuncSetAttribute(k_solve_cam, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(k_solve_cam<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(k_frame_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     h->attrs_set = true;
   }
@@ -749,13 +749,18 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius) {
     ST(allreduce(h, h->d_S_sum.p, n, ncclSum_));
   }
   {
-    const size_t need = (size_t)(C + 1) * std::max(C, 1) * sizeof(double);
-    const int in_smem = need <= 200 * 1024;
+    const size_t need = ((size_t)C * (C + 1) / 2 + C + 1) * sizeof(double);   // packed lower triangle + rhs row
+    const bool packed = need <= 200 * 1024;
     {
       KScope ks(h, KC_SOLVE);
-      k_solve_cam<<<1, 1024, in_smem ? need : 0, h->stream>>>(C, in_smem, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc.p, h->d_gc.p, h->d_S_sum.p,
-                                                           h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
-                                                           h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, h->d_fail.p);
+      if (packed)
+        k_solve_cam<true><<<1, CH_THREADS, need, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc.p, h->d_gc.p, h->d_S_sum.p,
+                                                              h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
+                                                              h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, h->d_fail.p);
+      else
+        k_solve_cam<false><<<1, CH_THREADS, 0, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc.p, h->d_gc.p, h->d_S_sum.p,
+                                                            h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
+                                                            h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, h->d_fail.p);
     }
     CU(cudaGetLastError());
   }
@@ -809,17 +814,17 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
   };
   double t0 = now_s();
   ST(launch_jacobian(h, o.use_loss));
+  {
+    KScope ks(h, KC_OTHER);
+    k_jacobi_scale<<<(std::max(h->C, h->nslots * 6) + 127) / 128, 128, 0, h->stream>>>(h->nslots, h->C, o.jacobi_scaling, h->d_Hcc.p, h->d_Hff.p, h->d_scale_c.p, h->d_scale_f.p);
+  }
+  CU(cudaGetLastError());
   ST(read_scalars(h));
   S.t_jacobian += now_s() - t0; S.n_jacobian_evals++;
   double cost = h->h_scal[0];
   double x_norm = std::sqrt(h->h_scal[1] + h->h_scal[9]);
   double gmax = std::max(h->h_scal[2], h->h_scal[8]);
   S.initial_cost = cost;
-  {
-    KScope ks(h, KC_OTHER);
-    k_jacobi_scale<<<(std::max(h->C, h->nslots * 6) + 127) / 128, 128, 0, h->stream>>>(h->nslots, h->C, o.jacobi_scaling, h->d_Hcc.p, h->d_Hff.p, h->d_scale_c.p, h->d_scale_f.p);
-  }
-  CU(cudaGetLastError());
   double radius = o.initial_trust_region_radius, decrease_factor = 2.0;
   log_row(cost, 0, gmax, 0, 0, radius);
   S.num_successful = 1;
@@ -828,15 +833,33 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
     return MCC_OK;
   };
   if (gmax <= o.gradient_tolerance) return finish(0, 0, gmax);
+  // After an accepted step the Jacobian pass at the new point is only ENQUEUED; its scalars (cost, gradient norm)
+  // are read together with the next step's, so an iteration costs one host synchronisation.  If the gradient
+  // tolerance turns out to be met, the speculative step is simply dropped.
+  bool pending = false;
+  double p_cost_change = 0, p_step_norm = 0, p_ratio = 0;
+  auto absorb_pending = [&]() {
+    cost = h->h_scal[0];
+    gmax = std::max(h->h_scal[2], h->h_scal[8]);
+    S.num_successful++;
+    log_row(cost, p_cost_change, gmax, p_step_norm, p_ratio, radius);
+    pending = false;
+  };
   int invalid_run = 0, iter = 0;
   while (true) {
-    if (iter >= o.max_num_iterations) return finish(1, 3, iter);
+    if (iter >= o.max_num_iterations) {
+      if (pending) { ST(read_scalars(h)); absorb_pending(); if (gmax <= o.gradient_tolerance) return finish(0, 0, gmax); }
+      return finish(1, 3, iter);
+    }
     iter++;
     t0 = now_s();
     ST(launch_step(h, o, radius));
     ST(read_scalars(h));
-    const double dt = now_s() - t0;
-    S.t_linear += dt; S.n_linear_solves++; S.n_residual_evals++;
+    S.t_linear += now_s() - t0; S.n_linear_solves++; S.n_residual_evals++;
+    if (pending) {
+      absorb_pending();
+      if (gmax <= o.gradient_tolerance) return finish(0, 0, gmax);
+    }
     const int flags = *h->h_fail;
     const double new_cost = h->h_scal[3];
     const double mcc = h->h_scal[4] + h->h_scal[10];
@@ -863,21 +886,19 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
       radius = radius / std::max(1.0 / 3.0, 1.0 - std::pow(2.0 * ratio - 1.0, 3));
       radius = std::min(o.max_trust_region_radius, radius);
       decrease_factor = 2.0;
-      t0 = now_s();
       ST(launch_jacobian(h, o.use_loss));
-      ST(read_scalars(h));
-      S.t_jacobian += now_s() - t0; S.n_jacobian_evals++;
-      cost = h->h_scal[0];
-      gmax = std::max(h->h_scal[2], h->h_scal[8]);
-      S.num_successful++;
-      log_row(cost, cost_change, gmax, step_norm, ratio, radius);
-      if (gmax <= o.gradient_tolerance) return finish(0, 0, gmax);
+      S.n_jacobian_evals++;
+      pending = true;
+      p_cost_change = cost_change; p_step_norm = step_norm; p_ratio = ratio;
     } else {
       radius /= decrease_factor; decrease_factor *= 2.0;
       S.num_unsuccessful++;
       log_row(cost, cost_change, 0.0, step_norm, ratio, radius);
     }
-    if (radius < o.min_trust_region_radius) return finish(0, 5, radius);
+    if (radius < o.min_trust_region_radius) {
+      if (pending) { ST(read_scalars(h)); absorb_pending(); }
+      return finish(0, 5, radius);
+    }
   }
 }
 
