@@ -258,7 +258,11 @@ struct mcc_handle {
   DBuf<double> d_aos_w, d_aos_i, d_X, d_Y, d_Z, d_U, d_V, d_res;
   DBuf<uint8_t> d_mask;
   DBuf<Tile> d_tiles;
-  DBuf<int> d_gto, d_lut, d_col_param, d_fail;
+  DBuf<int> d_gto, d_lut, d_col_param, d_fail, d_hff_tab, d_cam_tiles, d_cam_chunk0;
+  DBuf<int2> d_hfc_tab;
+  DBuf<CcChunk> d_cc_chunks;
+  DBuf<double> d_w_f;
+  int ncc_chunks = 0, cc_maxne = 1;
   DBuf<CamMeta> d_cams;
   DBuf<CcEntry> d_cc;
   DBuf<int2> d_colmap;
@@ -362,7 +366,6 @@ mcc_status ensure_device(mcc_handle* h) {
     CU(cudaFuncSetAttribute(k_tile_normal<27>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_schur_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(k_solve_cam<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    CU(cudaFuncSetAttribute(k_frame_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     h->attrs_set = true;
   }
   return MCC_OK;
@@ -470,6 +473,25 @@ mcc_status build_structure(mcc_handle* h) {
     }
   }
   h->E = (int)cc.size();
+  // direct gather tables for the frame blocks
+  std::vector<int> hff_tab((size_t)42 * ncam, 0);
+  for (int ent = 0; ent < 42; ent++) {
+    const int a = ent / 7, b = ent % 7;
+    for (int k = 0; k < ncam; k++) hff_tab[(size_t)ent * ncam + k] = lut[cm[k].lut_off + (cm[k].pose_col + a) * MAXC + (b < 6 ? cm[k].pose_col + b : cm[k].r_col)];
+  }
+  std::vector<int2> hfc_tab((size_t)6 * std::max(C, 1), make_int2(0, 0));
+  for (int a = 0; a < 6; a++)
+    for (int c = 0; c < C; c++) {
+      const int2 cmap = colmap[c];
+      hfc_tab[(size_t)a * C + c] = make_int2(cmap.x, lut[cm[cmap.x].lut_off + cmap.y * MAXC + cm[cmap.x].pose_col + a]);
+    }
+  // entry range of every camera in cc[] (entries were pushed camera by camera)
+  std::vector<int> cc_e0(ncam + 1, 0);
+  {
+    size_t e = 0;
+    for (int k = 0; k < ncam; k++) { cc_e0[k] = (int)e; while (e < cc.size() && cc[e].cam == k) e++; }
+    cc_e0[ncam] = (int)e;
+  }
 
   // observation offsets, active frames, tiles
   h->group_obs0.assign((size_t)F * ncam + 1, 0);
@@ -516,6 +538,27 @@ mcc_status build_structure(mcc_handle* h) {
   }
   gto[h->ngroups] = (int)tiles.size();
   h->ntiles = (int)tiles.size();
+  // per-camera tile lists (tile order = frame order) cut into chunks for the camera-camera reduction
+  std::vector<int> cam_tiles;
+  std::vector<CcChunk> cc_chunks;
+  std::vector<int> cam_chunk0(ncam + 1, 0);
+  h->cc_maxne = 1;
+  {
+    std::vector<std::vector<int>> per(ncam);
+    for (int t = 0; t < h->ntiles; t++) per[tiles[t].group % ncam].push_back(t);
+    for (int k = 0; k < ncam; k++) {
+      cam_chunk0[k] = (int)cc_chunks.size();
+      const int ne = cc_e0[k + 1] - cc_e0[k];
+      h->cc_maxne = std::max(h->cc_maxne, ne);
+      if (ne == 0) continue;
+      const int first = (int)cam_tiles.size();
+      cam_tiles.insert(cam_tiles.end(), per[k].begin(), per[k].end());
+      for (int o = 0; o < (int)per[k].size(); o += CC_CHUNK)
+        cc_chunks.push_back(CcChunk{k, first + o, std::min(CC_CHUNK, (int)per[k].size() - o), cc_e0[k], ne});
+    }
+    cam_chunk0[ncam] = (int)cc_chunks.size();
+  }
+  h->ncc_chunks = (int)cc_chunks.size();
 
   const int NT = (C + 1 + SY_T - 1) / SY_T;
   h->npairs = NT * (NT + 1) / 2;
@@ -525,7 +568,7 @@ mcc_status build_structure(mcc_handle* h) {
   CU(cudaGetDeviceProperties(&prop, h->device));
   const int sms = prop.multiProcessorCount;
   h->sy_gx = std::max(1, std::min((h->nslots + SY_FB - 1) / SY_FB, std::max(1, (2 * sms) / h->sy_gy)));
-  h->asm_grid = std::max(1, std::min(h->nslots, 4 * sms));
+  h->asm_grid = 1;
 
   // upload structure
   auto up = [&](auto& buf, const auto& vec) -> cudaError_t {
@@ -539,6 +582,12 @@ mcc_status build_structure(mcc_handle* h) {
   CU(up(h->d_lut, lut));
   CU(up(h->d_colmap, colmap));
   CU(up(h->d_cc, cc));
+  CU(up(h->d_hff_tab, hff_tab));
+  CU(up(h->d_hfc_tab, hfc_tab));
+  CU(up(h->d_cam_tiles, cam_tiles));
+  CU(up(h->d_cc_chunks, cc_chunks));
+  CU(up(h->d_cam_chunk0, cam_chunk0));
+  CU(h->d_w_f.reserve(std::max(h->nslots, 1)));
   CU(up(h->d_tiles, tiles));
   CU(up(h->d_gto, gto));
   CU(up(h->d_col_param, h->col_param));
@@ -549,7 +598,7 @@ mcc_status build_structure(mcc_handle* h) {
   CU(h->d_Hff.reserve(ns * 36)); CU(h->d_gf.reserve(ns * 6)); CU(h->d_Hfc.reserve(ns * 6 * std::max(C, 1))); CU(h->d_Lf.reserve(ns * 36));
   CU(h->d_cost_f.reserve(ns)); CU(h->d_gmax_f.reserve(ns)); CU(h->d_xn2_f.reserve(ns)); CU(h->d_newcost_f.reserve(ns));
   CU(h->d_mcc_f.reserve(ns)); CU(h->d_dx2_f.reserve(ns)); CU(h->d_xn2c_f.reserve(ns));
-  CU(h->d_cc_part.reserve((size_t)h->asm_grid * std::max(h->E, 1))); CU(h->d_cc_sum.reserve(std::max(h->E, 1)));
+  CU(h->d_cc_part.reserve((size_t)std::max(h->ncc_chunks, 1) * h->cc_maxne)); CU(h->d_cc_sum.reserve(std::max(h->E, 1)));
   CU(h->d_Hcc.reserve((size_t)std::max(C, 1) * std::max(C, 1))); CU(h->d_gc.reserve(std::max(C, 1)));
   CU(h->d_scale_c.reserve(std::max(C, 1))); CU(h->d_scale_f.reserve(ns * 6));
   CU(h->d_S_part.reserve((size_t)h->sy_gx * h->npairs * SY_T * SY_T)); CU(h->d_S_sum.reserve((size_t)h->npairs * SY_T * SY_T));
@@ -678,17 +727,23 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss) {
 #undef MCC_LAUNCH_TILE_NORMAL
     CU(cudaGetLastError());
   }
-  {
+  if (h->nslots) {
     KScope ks(h, KC_ASSEMBLE);
-    k_frame_assemble<<<h->asm_grid, 128, std::max(h->E, 1) * sizeof(double), h->stream>>>(
-      h->nslots, h->ncam(), h->C, h->E, h->d_gto.p, h->d_cams.p, h->d_lut.p, h->d_cc.p, h->d_colmap.p, h->d_G.p, h->gstride, h->d_tile_s.p,
-      h->d_pose[which].p, use_loss, h->d_Hff.p, h->d_gf.p, h->d_Hfc.p, h->d_cost_f.p, h->d_gmax_f.p, h->d_xn2_f.p, h->d_cc_part.p);
+    k_frame_blocks<<<h->nslots, 128, 0, h->stream>>>(h->nslots, h->ncam(), h->C, h->d_gto.p, h->d_hff_tab.p, h->d_hfc_tab.p, h->d_G.p, h->gstride,
+                                                     h->d_tile_s.p, h->d_pose[which].p, use_loss, h->d_Hff.p, h->d_gf.p, h->d_Hfc.p, h->d_cost_f.p,
+                                                     h->d_gmax_f.p, h->d_xn2_f.p, h->d_w_f.p);
   }
   CU(cudaGetLastError());
   if (h->E) {
+    if (h->ncc_chunks) {
+      KScope ks(h, KC_ASSEMBLE);
+      k_cc_partial<<<h->ncc_chunks, 128, 0, h->stream>>>(h->ncam(), h->d_cc_chunks.p, h->d_cam_tiles.p, h->d_tiles.p, h->d_cc.p, h->d_w_f.p, h->d_G.p,
+                                                         h->gstride, h->cc_maxne, h->d_cc_part.p);
+    }
+    CU(cudaGetLastError());
     {
       KScope ks(h, KC_REDUCE);
-      k_reduce_rows<<<(h->E + 127) / 128, 128, 0, h->stream>>>(h->asm_grid, h->E, h->d_cc_part.p, h->d_cc_sum.p);
+      k_cc_reduce<<<(h->E + 127) / 128, 128, 0, h->stream>>>(h->E, h->d_cc.p, h->d_cam_chunk0.p, h->d_cc_chunks.p, h->cc_maxne, h->d_cc_part.p, h->d_cc_sum.p);
     }
     CU(cudaGetLastError());
   }
@@ -946,7 +1001,8 @@ void mcc_destroy(mcc_handle* h) {
                         &h->d_S_sum, &h->d_M, &h->d_yc, &h->d_ysc, &h->d_scal};
   for (auto* b : dd) b->release();
   h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_lut.release(); h->d_col_param.release(); h->d_fail.release();
-  h->d_cams.release(); h->d_cc.release(); h->d_colmap.release();
+  h->d_cams.release(); h->d_cc.release(); h->d_colmap.release(); h->d_hff_tab.release(); h->d_hfc_tab.release();
+  h->d_cam_tiles.release(); h->d_cam_chunk0.release(); h->d_cc_chunks.release(); h->d_w_f.release();
   h->world.release(); h->image.release();
   if (h->h_scal) cudaFreeHost(h->h_scal);
   if (h->h_fail) cudaFreeHost(h->h_fail);
