@@ -172,6 +172,13 @@ mcc_status mcc_eval_normal_blocks(mcc_handle* h, int use_loss, double* cost, dou
 mcc_status mcc_comm_unique_id(unsigned char id[MCC_UNIQUE_ID_BYTES]);
 mcc_status mcc_comm_init(mcc_handle* h, int nranks, int rank, const unsigned char id[MCC_UNIQUE_ID_BYTES]);
 
+/* How the per-tile Gram matrix [J r]^T [J r] is contracted (no reference counterpart: Ceres forms J^T J on the CPU).
+ * 0 (default): FP64 FMA pipe, 3x3 register blocks per lane.  1: FP64 tensor pipe, mma.sync.m8n8k4 (DMMA).
+ * Both are IEEE fp64 with fused multiply-adds; only the summation order differs.  The environment variable
+ * MCC_GRAM=dmma|fma sets the initial mode of new handles. */
+mcc_status mcc_set_gram_mode(mcc_handle* h, int mode);
+int mcc_get_gram_mode(const mcc_handle* h);
+
 /* Measurement hooks for bench.py (no reference counterpart: Ceres only prints wall-clock phase times,
  * calibrator.cpp:312).  mcc_timer_start/stop bracket a region with CUDA events on the handle's stream (the
  * stream every kernel of this library is launched on).  With kernel timing enabled every launch is bracketed

@@ -72,7 +72,7 @@ SYMBOLS = ["mcc_version", "mcc_default_options", "mcc_summary_size", "mcc_create
            "mcc_set_mask", "mcc_num_reduced_cam_cols", "mcc_num_active_frames", "mcc_eval_normal_blocks", "mcc_comm_unique_id", "mcc_comm_init",
            "mcc_transform_to_rvec_tvec", "mcc_rvec_tvec_to_transform", "mcc_timer_start", "mcc_timer_stop", "mcc_set_kernel_timing",
            "mcc_num_kernel_classes", "mcc_kernel_class_name", "mcc_get_kernel_times", "mcc_measure_fp64_peak",
-           "mcc_reprojection_cost_noalloc"]
+           "mcc_reprojection_cost_noalloc", "mcc_set_gram_mode", "mcc_get_gram_mode"]
 
 
 def build(force: bool = False) -> str:
@@ -140,6 +140,8 @@ def lib():
     L.mcc_kernel_class_name.restype = C.c_char_p
     L.mcc_get_kernel_times.argtypes = [vp, dp, C.POINTER(C.c_longlong), C.c_int]
     L.mcc_measure_fp64_peak.argtypes = [C.c_int, dp]
+    L.mcc_set_gram_mode.argtypes = [vp, C.c_int]
+    L.mcc_get_gram_mode.argtypes = [vp]
     L.mcc_reprojection_cost_noalloc.argtypes = [C.c_int, C.c_int] + [vp, vp, C.c_size_t] + [vp] * 8 + [C.c_char_p, C.c_size_t]
     assert L.mcc_summary_size() == C.sizeof(Summary), (L.mcc_summary_size(), C.sizeof(Summary))
     _lib = L
@@ -360,6 +362,10 @@ class Calibrator:
         Hff = np.zeros((max(ns, 1), 6, 6)); gf = np.zeros((max(ns, 1), 6)); Hfc = np.zeros((max(ns, 1), 6, max(Cc, 1))); ids = np.zeros(max(ns, 1), dtype=np.int32)
         self._check(self._L.mcc_eval_normal_blocks(self.h, int(use_loss), C.byref(cost), _dp(Hcc) if Cc else None, _dp(gc), _dp(Hff), _dp(gf), _dp(Hfc), _ip(ids)))
         return dict(cost=cost.value, Hcc=Hcc, gc=gc[:Cc], Hff=Hff[:ns], gf=gf[:ns], Hfc=Hfc.reshape(-1)[:ns * 6 * Cc].reshape(ns, 6, Cc), frames=ids[:ns])
+
+    def setGramMode(self, mode: int):
+        """0: FP64 FMA register blocks (default); 1: FP64 mma.sync (DMMA) tiles"""
+        self._check(self._L.mcc_set_gram_mode(self.h, int(mode)))
 
     def timerStart(self):
         self._check(self._L.mcc_timer_start(self.h))

@@ -18,6 +18,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -162,6 +163,22 @@ struct DBuf {
     if (e == cudaSuccess) cap = n;
     return e;
   }
+  // grow keeping the first `keep` elements (device-to-device copy on stream st)
+  cudaError_t reserve_keep(size_t n, size_t keep, cudaStream_t st) {
+    if (n <= cap) return cudaSuccess;
+    const size_t ncap = std::max(n, cap + cap / 2);
+    T* q = nullptr;
+    cudaError_t e = cudaMalloc((void**)&q, std::max<size_t>(ncap, 1) * sizeof(T));
+    if (e != cudaSuccess) return e;
+    if (p && keep) {
+      e = cudaMemcpyAsync(q, p, keep * sizeof(T), cudaMemcpyDeviceToDevice, st);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+      if (e != cudaSuccess) { cudaFree(q); return e; }
+    }
+    if (p) cudaFree(p);
+    p = q; cap = ncap;
+    return cudaSuccess;
+  }
   void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 template <typename T>
@@ -238,8 +255,11 @@ struct mcc_handle {
   std::vector<int> npts;               // [F * ncam]
   PinBuf<double> world, image;         // AoS staging: 3N, 2N
   std::vector<double> poses;           // 16 F
-  std::vector<uint8_t> mask;           // N
+  std::vector<uint8_t> mask;           // N, materialised lazily: while mask_all_one every point is valid
+  bool mask_all_one = true;
   size_t nobs = 0;
+  size_t host_count = 0;               // observations [0, host_count) are present in the host staging buffers
+  size_t dev_count = 0;                // observations [0, dev_count) are present in the device AoS buffers
   int nframes = 0;
   std::vector<double> params;          // calibrator.cpp:36-46 layout
   bool params_valid = false;
@@ -273,6 +293,9 @@ struct mcc_handle {
   double* h_scal = nullptr;            // pinned mirror of d_scal
   int* h_fail = nullptr;
   int asm_grid = 0, sy_gx = 0, sy_gy = 0;
+  int sms = 0;
+  int gram_mode = 0;                   // 0: FP64 FMA 3x3 register blocks, 1: FP64 mma.sync (DMMA) 8x8 tiles
+  int nt8 = 3;
   bool attrs_set = false;
   long long launches = 0, h2d = 0, d2h = 0;
   // optional per-launch timing
@@ -316,6 +339,11 @@ mcc_status fail(mcc_handle* h, mcc_status st, const char* fmt, ...) {
     int r_ = (call);                                                                                                  \
     if (r_ != 0) return fail(h, MCC_ERR_NCCL, "%s failed: %s", #call, nccl().GetErrorString ? nccl().GetErrorString(r_) : "?"); \
   } while (0)
+
+// host mask, created on first need (addPoints marks every point valid, calibrator.cpp:246)
+void materialize_mask(mcc_handle* h) {
+  if (h->mask.size() != h->nobs) h->mask.resize(h->nobs, 1);
+}
 
 struct KScope {
   mcc_handle* h;
@@ -364,6 +392,8 @@ mcc_status ensure_device(mcc_handle* h) {
     CU(cudaFuncSetAttribute(k_tile_normal<15>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_tile_normal<21>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CU(cudaFuncSetAttribute(k_tile_normal<27>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CU((cudaFuncSetAttribute(k_tile_normal_mma<28, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
+    CU((cudaFuncSetAttribute(k_tile_normal_mma<36, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
     CU(cudaFuncSetAttribute(k_schur_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(k_solve_cam<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     h->attrs_set = true;
@@ -422,7 +452,7 @@ mcc_status build_structure(mcc_handle* h) {
   // camera metadata + Gram lookup tables
   std::vector<CamMeta> cm(ncam);
   std::vector<int> lut((size_t)ncam * MAXC * MAXC, 0);
-  int max_nb = 1, max_nblk = 1;
+  int max_nb = 1, max_nblk = 1, max_cols = 1;
   for (int k = 0; k < ncam; k++) {
     const CamHost& c = h->cams[k];
     CamMeta& m = cm[k];
@@ -439,18 +469,33 @@ mcc_status build_structure(mcc_handle* h) {
     for (int j = 0; j < c.nparam(); j++) m.red_col[j] = h->cam_col[h->intr_off[k] + j];
     if (k > 0) for (int j = 0; j < 6; j++) m.red_col[m.ext_col + j] = h->cam_col[h->ext_off[k] + j];
     m.lut_off = k * MAXC * MAXC;
+    if (c.active) { max_nb = std::max(max_nb, m.nb); max_nblk = std::max(max_nblk, m.nblk); max_cols = std::max(max_cols, m.ncols); }
+  }
+  h->nt8 = max_cols <= 24 ? 3 : 4;
+  for (int k = 0; k < ncam; k++) {
+    const CamMeta& m = cm[k];
     for (int i = 0; i < m.ncols; i++)
       for (int j = 0; j < m.ncols; j++) {
-        const int bi = i / 3, bj = j / 3;
         int o;
-        if (bi <= bj) o = tri_index(bi, bj, m.nb) * 9 + (i % 3) * 3 + (j % 3);
-        else o = tri_index(bj, bi, m.nb) * 9 + (j % 3) * 3 + (i % 3);
+        if (h->gram_mode == 0) {
+          const int bi = i / 3, bj = j / 3;
+          if (bi <= bj) o = tri_index(bi, bj, m.nb) * 9 + (i % 3) * 3 + (j % 3);
+          else o = tri_index(bj, bi, m.nb) * 9 + (j % 3) * 3 + (i % 3);
+        } else {
+          const int bi = i / 8, bj = j / 8;
+          if (bi <= bj) o = tri_index(bi, bj, h->nt8) * 64 + (i % 8) * 8 + (j % 8);
+          else o = tri_index(bj, bi, h->nt8) * 64 + (j % 8) * 8 + (i % 8);
+        }
         lut[m.lut_off + i * MAXC + j] = o;
       }
-    if (c.active) { max_nb = std::max(max_nb, m.nb); max_nblk = std::max(max_nblk, m.nblk); }
   }
-  h->gstride = 9 * max_nblk;
-  h->rowstride = max_nb <= 5 ? 15 : (max_nb <= 7 ? 21 : 27);   // the instantiations of k_tile_normal<RS>
+  if (h->gram_mode == 0) {
+    h->gstride = 9 * max_nblk;
+    h->rowstride = max_nb <= 5 ? 15 : (max_nb <= 7 ? 21 : 27);   // the instantiations of k_tile_normal<RS>
+  } else {
+    h->gstride = 64 * h->nt8 * (h->nt8 + 1) / 2;
+    h->rowstride = h->nt8 == 3 ? 28 : 36;                        // k_tile_normal_mma<RS, NT8>
+  }
 
   // reduced column -> (camera, local column)
   std::vector<int2> colmap(std::max(C, 1));
@@ -508,7 +553,8 @@ mcc_status build_structure(mcc_handle* h) {
     for (int k = 0; k < ncam; k++) {
       if (!h->cams[k].active) continue;
       const size_t o0 = h->group_obs0[(size_t)f * ncam + k], n = h->npts[(size_t)f * ncam + k];
-      for (size_t i = 0; i < n; i++) nv += h->mask[o0 + i] != 0;
+      if (h->mask_all_one) nv += (long long)n;
+      else for (size_t i = 0; i < n; i++) nv += h->mask[o0 + i] != 0;
     }
     if (nv > 0) { h->frame_slot[f] = (int)h->slot_frame.size(); h->slot_frame.push_back(f); h->nres += 2 * nv; }
   }
@@ -564,9 +610,8 @@ mcc_status build_structure(mcc_handle* h) {
   h->npairs = NT * (NT + 1) / 2;
   h->LD = NT * SY_T;
   h->sy_gy = (h->npairs + SY_THREADS - 1) / SY_THREADS;
-  cudaDeviceProp prop;
-  CU(cudaGetDeviceProperties(&prop, h->device));
-  const int sms = prop.multiProcessorCount;
+  if (h->sms <= 0) CU(cudaDeviceGetAttribute(&h->sms, cudaDevAttrMultiProcessorCount, h->device));
+  const int sms = h->sms;
   h->sy_gx = std::max(1, std::min((h->nslots + SY_FB - 1) / SY_FB, std::max(1, (2 * sms) / h->sy_gy)));
   h->asm_grid = 1;
 
@@ -614,12 +659,17 @@ mcc_status build_structure(mcc_handle* h) {
 mcc_status upload_obs(mcc_handle* h) {
   const size_t n = h->nobs;
   if (h->obs_dirty) {
-    CU(h->d_aos_w.reserve(3 * n)); CU(h->d_aos_i.reserve(2 * n));
     CU(h->d_X.reserve(n)); CU(h->d_Y.reserve(n)); CU(h->d_Z.reserve(n)); CU(h->d_U.reserve(n)); CU(h->d_V.reserve(n));
+    CU(h->d_aos_w.reserve_keep(3 * n, 3 * h->dev_count, h->stream)); CU(h->d_aos_i.reserve_keep(2 * n, 2 * h->dev_count, h->stream));
     if (n) {
-      CU(cudaMemcpyAsync(h->d_aos_w.p, h->world.p, 3 * n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-      CU(cudaMemcpyAsync(h->d_aos_i.p, h->image.p, 2 * n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-      h->h2d += 5 * n * sizeof(double);
+      if (h->dev_count < n) {
+        // only what is not on the device yet (frames added from pinned memory went there directly)
+        const size_t o = h->dev_count, m = n - o;
+        CU(cudaMemcpyAsync(h->d_aos_w.p + 3 * o, h->world.p + 3 * o, 3 * m * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        CU(cudaMemcpyAsync(h->d_aos_i.p + 2 * o, h->image.p + 2 * o, 2 * m * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        h->h2d += 5 * m * sizeof(double);
+        h->dev_count = n;
+      }
       {
         KScope ks(h, KC_OTHER);
         k_aos_to_soa<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(n, h->d_aos_w.p, h->d_aos_i.p, h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p);
@@ -630,7 +680,10 @@ mcc_status upload_obs(mcc_handle* h) {
   }
   if (h->mask_dirty) {
     CU(h->d_mask.reserve(n));
-    if (n) { CU(cudaMemcpyAsync(h->d_mask.p, h->mask.data(), n, cudaMemcpyHostToDevice, h->stream)); h->h2d += n; }
+    if (n) {
+      if (h->mask_all_one) CU(cudaMemsetAsync(h->d_mask.p, 1, n, h->stream));
+      else { CU(cudaMemcpyAsync(h->d_mask.p, h->mask.data(), n, cudaMemcpyHostToDevice, h->stream)); h->h2d += n; }
+    }
     h->mask_dirty = false;
   }
   return MCC_OK;
@@ -721,9 +774,14 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss) {
 #define MCC_LAUNCH_TILE_NORMAL(RS)                                                                                                          \
     k_tile_normal<RS><<<grid, K1_WARPS * 32, smem, h->stream>>>(h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, \
                                                                  h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p, h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p)
-    if (h->rowstride == 15) MCC_LAUNCH_TILE_NORMAL(15);
+#define MCC_LAUNCH_TILE_MMA(RS, NT)                                                                                                         \
+    k_tile_normal_mma<RS, NT><<<grid, K1_WARPS * 32, smem, h->stream>>>(h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, \
+                                                                         h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p, h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p)
+    if (h->gram_mode == 1) { if (h->nt8 == 3) MCC_LAUNCH_TILE_MMA(28, 3); else MCC_LAUNCH_TILE_MMA(36, 4); }
+    else if (h->rowstride == 15) MCC_LAUNCH_TILE_NORMAL(15);
     else if (h->rowstride == 21) MCC_LAUNCH_TILE_NORMAL(21);
     else MCC_LAUNCH_TILE_NORMAL(27);
+#undef MCC_LAUNCH_TILE_MMA
 #undef MCC_LAUNCH_TILE_NORMAL
     CU(cudaGetLastError());
   }
@@ -988,7 +1046,9 @@ int mcc_summary_size(void) { return (int)sizeof(mcc_summary); }
 mcc_status mcc_create(mcc_handle** out) {
   if (!out) return MCC_ERR_BAD_ARG;
   *out = new (std::nothrow) mcc_handle();
-  return *out ? MCC_OK : MCC_ERR_BAD_ARG;
+  if (!*out) return MCC_ERR_BAD_ARG;
+  if (const char* e = std::getenv("MCC_GRAM")) (*out)->gram_mode = (std::strcmp(e, "dmma") == 0) ? 1 : 0;
+  return MCC_OK;
 }
 
 void mcc_destroy(mcc_handle* h) {
@@ -1072,12 +1132,44 @@ mcc_status mcc_add_frames(mcc_handle* h, int nframes, int ncam, const int* npts,
   size_t n = 0;
   for (size_t i = 0; i < (size_t)nframes * ncam; i++) { if (npts[i] < 0) return fail(h, MCC_ERR_BAD_ARG, "negative point count"); n += npts[i]; }
   if (n && (!world_xyz || !image_uv)) return fail(h, MCC_ERR_BAD_ARG, "null point arrays");
-  if (!h->world.reserve(3 * (h->nobs + n), 3 * h->nobs) || !h->image.reserve(2 * (h->nobs + n), 2 * h->nobs)) return fail(h, MCC_ERR_BAD_ARG, "out of host memory");
-  parallel_memcpy(h->world.p + 3 * h->nobs, world_xyz, 3 * n * sizeof(double));
-  parallel_memcpy(h->image.p + 2 * h->nobs, image_uv, 2 * n * sizeof(double));
+  // Where do the points go?  If the caller's arrays are page-locked (cudaHostAlloc / cudaHostRegister) and the
+  // device copy is in step, they are DMA'd straight into the device AoS buffers -- no host staging pass.  Otherwise
+  // they are copied into the handle's own pinned staging buffers and uploaded by the next run.  Either way the
+  // caller's memory is no longer referenced when this returns.
+  bool direct = false;
+  if (n >= 4096 && h->dev_count == h->nobs) {
+    cudaPointerAttributes aw, ai;
+    const bool pw = cudaPointerGetAttributes(&aw, world_xyz) == cudaSuccess && aw.type == cudaMemoryTypeHost;
+    const bool pi = cudaPointerGetAttributes(&ai, image_uv) == cudaSuccess && ai.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    direct = pw && pi && ensure_device(h) == MCC_OK;
+  }
+  if (direct) {
+    const size_t o = h->nobs;
+    CU(h->d_aos_w.reserve_keep(3 * (o + n), 3 * o, h->stream));
+    CU(h->d_aos_i.reserve_keep(2 * (o + n), 2 * o, h->stream));
+    CU(cudaMemcpyAsync(h->d_aos_w.p + 3 * o, world_xyz, 3 * n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->d_aos_i.p + 2 * o, image_uv, 2 * n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    h->h2d += 5 * n * sizeof(double);
+    h->dev_count = o + n;
+  } else {
+    if (!h->world.reserve(3 * (h->nobs + n), 3 * h->host_count) || !h->image.reserve(2 * (h->nobs + n), 2 * h->host_count)) return fail(h, MCC_ERR_BAD_ARG, "out of host memory");
+    if (h->host_count < h->nobs) {
+      // earlier frames went to the device only: bring them back so that the staging buffers are whole again
+      const size_t o = h->host_count, m = h->nobs - o;
+      CU(cudaMemcpyAsync(h->world.p + 3 * o, h->d_aos_w.p + 3 * o, 3 * m * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+      CU(cudaMemcpyAsync(h->image.p + 2 * o, h->d_aos_i.p + 2 * o, 2 * m * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+      CU(cudaStreamSynchronize(h->stream));
+      h->d2h += 5 * m * sizeof(double);
+    }
+    parallel_memcpy(h->world.p + 3 * h->nobs, world_xyz, 3 * n * sizeof(double));
+    parallel_memcpy(h->image.p + 2 * h->nobs, image_uv, 2 * n * sizeof(double));
+    h->host_count = h->nobs + n;
+  }
   h->npts.insert(h->npts.end(), npts, npts + (size_t)nframes * ncam);
   h->poses.insert(h->poses.end(), poses, poses + 16 * (size_t)nframes);
-  h->mask.resize(h->nobs + n, 1);
+  if (!h->mask_all_one) h->mask.resize(h->nobs + n, 1);
   h->nobs += n;
   h->nframes += nframes;
   h->structure_dirty = h->obs_dirty = h->mask_dirty = true;
@@ -1102,8 +1194,8 @@ mcc_status mcc_add_frame(mcc_handle* h, int ncam, const int* npts, const double*
 
 mcc_status mcc_clear_frames(mcc_handle* h) {
   if (!h) return MCC_ERR_BAD_ARG;
-  h->npts.clear(); h->poses.clear(); h->mask.clear();
-  h->nobs = 0; h->nframes = 0;
+  h->npts.clear(); h->poses.clear(); h->mask.clear(); h->mask_all_one = true;
+  h->nobs = 0; h->nframes = 0; h->host_count = 0; h->dev_count = 0;
   h->structure_dirty = h->obs_dirty = h->mask_dirty = true;
   h->params_valid = false;
   return MCC_OK;
@@ -1215,7 +1307,7 @@ long long mcc_num_residuals(const mcc_handle* hc) {
   for (int f = 0; f < h->nframes; f++)
     for (int k = 0; k < h->ncam(); k++) {
       const int np = h->npts[(size_t)f * h->ncam() + k];
-      if (h->cams[k].active) for (int i = 0; i < np; i++) n += h->mask[o + i] != 0;
+      if (h->cams[k].active) { if (h->mask_all_one) n += np; else for (int i = 0; i < np; i++) n += h->mask[o + i] != 0; }
       o += np;
     }
   return 2 * n;
@@ -1241,7 +1333,7 @@ mcc_status mcc_eval_residuals(mcc_handle* h, double* out_xy, size_t n_out) {
       const size_t o0 = h->group_obs0[(size_t)f * ncam + k];
       const int np = h->npts[(size_t)f * ncam + k];
       for (int i = 0; i < np; i++)
-        if (h->mask[o0 + i]) { out_xy[w++] = all[2 * (o0 + i)]; out_xy[w++] = all[2 * (o0 + i) + 1]; }
+        if (h->mask_all_one || h->mask[o0 + i]) { out_xy[w++] = all[2 * (o0 + i)]; out_xy[w++] = all[2 * (o0 + i) + 1]; }
     }
   }
   return MCC_OK;
@@ -1276,6 +1368,7 @@ mcc_status mcc_remove_outliers(mcc_handle* h, double max_err, long long* ndroppe
   h->d2h += all.size() * sizeof(double);
   const double m2 = max_err * max_err;
   long long dropped = 0;
+  materialize_mask(h);
   const int ncam = h->ncam();
   for (int s = 0; s < h->nslots; s++) {
     const int f = h->slot_frame[s];
@@ -1290,19 +1383,22 @@ mcc_status mcc_remove_outliers(mcc_handle* h, double max_err, long long* ndroppe
       }
     }
   }
-  if (dropped) { h->mask_dirty = true; h->structure_dirty = true; }
+  if (dropped) { h->mask_dirty = true; h->structure_dirty = true; h->mask_all_one = false; }
   if (ndropped) *ndropped = dropped;
   return MCC_OK;
 }
 
 mcc_status mcc_get_mask(const mcc_handle* h, uint8_t* out, size_t n) {
   if (!h || !out || n < h->nobs) return MCC_ERR_BAD_ARG;
-  std::memcpy(out, h->mask.data(), h->nobs);
+  if (h->mask_all_one) std::memset(out, 1, h->nobs);
+  else std::memcpy(out, h->mask.data(), h->nobs);
   return MCC_OK;
 }
 mcc_status mcc_set_mask(mcc_handle* h, const uint8_t* in, size_t n) {
   if (!h || !in || n != h->nobs) return MCC_ERR_BAD_ARG;
+  materialize_mask(h);
   std::memcpy(h->mask.data(), in, n);
+  h->mask_all_one = false;
   h->mask_dirty = true; h->structure_dirty = true;
   return MCC_OK;
 }
@@ -1353,6 +1449,13 @@ mcc_status mcc_comm_init(mcc_handle* h, int nranks, int rank, const unsigned cha
   h->nranks = nranks; h->rank = rank;
   return MCC_OK;
 }
+
+mcc_status mcc_set_gram_mode(mcc_handle* h, int mode) {
+  if (!h || (mode != 0 && mode != 1)) return MCC_ERR_BAD_ARG;
+  if (h->gram_mode != mode) { h->gram_mode = mode; h->structure_dirty = true; }
+  return MCC_OK;
+}
+int mcc_get_gram_mode(const mcc_handle* h) { return h ? h->gram_mode : -1; }
 
 mcc_status mcc_set_kernel_timing(mcc_handle* h, int enabled) {
   if (!h) return MCC_ERR_BAD_ARG;

@@ -12,7 +12,7 @@ rep = sys.argv[1]
 out = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv'], capture_output=True, text=True).stdout
 blocks = out.split('"Kernel Name"')
 which = int(sys.argv[2]) if len(sys.argv) > 2 else 0
-blk = '"Kernel Name"' + blocks[1 + which]
+blk = '"Kernel Name"' + blocks[1 + 2 * which]   # every kernel appears twice in the csv
 lines = blk.splitlines()
 r = list(csv.reader(io.StringIO('\n'.join(lines[1:]))))
 hdr = r[0]

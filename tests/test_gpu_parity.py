@@ -256,3 +256,33 @@ def test_error_conventions(small_rig):
         cal.addPoints(0, [np.zeros((0, 3))], [np.zeros((0, 2))], np.eye(4))   # camera-count mismatch (calibrator.cpp:236-240)
     assert e.value.status == -2
     cal.close()
+
+
+def test_pinned_and_pageable_inputs_agree(small_rig, c3_rig):
+    """mcc_add_frames DMAs page-locked caller arrays straight to the device and stages pageable ones on the host;
+    mixing both in one handle must give the bit-identical solve"""
+    import torch
+    from multicam_calibration_b200 import capi
+    from multicam_calibration_b200.rig import Rig
+    rig = c3_rig
+    ref = capi.calibrator_from_rig(rig, 0)
+    s0 = ref.runCalibration()
+    half = rig.num_frames // 2
+    a, b = rig.slice_frames(0, half), rig.slice_frames(half, rig.num_frames)
+    wp, ip = torch.from_numpy(a.world).pin_memory(), torch.from_numpy(a.image).pin_memory()
+    a_pinned = Rig(a.cameras, a.npts, wp.numpy(), ip.numpy(), a.poses)
+    cal = capi.Calibrator(0)
+    cal.setCameras(rig.cameras)
+    cal.addFrames(a_pinned)      # direct DMA
+    cal.addFrames(b)             # pageable -> staged (pulls the first half back into the staging buffers)
+    s1 = cal.runCalibration()
+    assert s1.final_cost == s0.final_cost and s1.num_iterations == s0.num_iterations
+    assert np.array_equal(cal.getParams(), ref.getParams())
+    # and again after clear, pageable first then pinned
+    cal.clearFrames()
+    wp2, ip2 = torch.from_numpy(b.world).pin_memory(), torch.from_numpy(b.image).pin_memory()
+    cal.addFrames(a)
+    cal.addFrames(Rig(b.cameras, b.npts, wp2.numpy(), ip2.numpy(), b.poses))
+    s2 = cal.runCalibration()
+    assert s2.final_cost == s0.final_cost and np.array_equal(cal.getParams(), ref.getParams())
+    cal.close(); ref.close()
