@@ -295,7 +295,6 @@ struct mcc_handle {
   int asm_grid = 0, sy_gx = 0, sy_gy = 0;
   int sms = 0;
   int gram_mode = 0;                   // 0: FP64 FMA 3x3 register blocks, 1: FP64 mma.sync (DMMA) 8x8 tiles
-  int nt8 = 3;
   bool attrs_set = false;
   long long launches = 0, h2d = 0, d2h = 0;
   // optional per-launch timing
@@ -389,11 +388,10 @@ mcc_status ensure_device(mcc_handle* h) {
   if (!h->h_scal) CU(cudaHostAlloc((void**)&h->h_scal, 32 * sizeof(double), cudaHostAllocDefault));
   if (!h->h_fail) CU(cudaHostAlloc((void**)&h->h_fail, sizeof(int), cudaHostAllocDefault));
   if (!h->attrs_set) {
-    CU(cudaFuncSetAttribute(k_tile_normal<15>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    CU(cudaFuncSetAttribute(k_tile_normal<21>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    CU(cudaFuncSetAttribute(k_tile_normal<27>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    CU((cudaFuncSetAttribute(k_tile_normal_mma<28, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
-    CU((cudaFuncSetAttribute(k_tile_normal_mma<36, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
+    CU((cudaFuncSetAttribute(k_tile_normal<15, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
+    CU((cudaFuncSetAttribute(k_tile_normal<21, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
+    CU((cudaFuncSetAttribute(k_tile_normal<20, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
+    CU((cudaFuncSetAttribute(k_tile_normal<28, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
     CU(cudaFuncSetAttribute(k_schur_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(k_solve_cam<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     h->attrs_set = true;
@@ -452,7 +450,7 @@ mcc_status build_structure(mcc_handle* h) {
   // camera metadata + Gram lookup tables
   std::vector<CamMeta> cm(ncam);
   std::vector<int> lut((size_t)ncam * MAXC * MAXC, 0);
-  int max_nb = 1, max_nblk = 1, max_cols = 1;
+  int max_nb = 1, max_nblk = 1, max_red_cols = 11;
   for (int k = 0; k < ncam; k++) {
     const CamHost& c = h->cams[k];
     CamMeta& m = cm[k];
@@ -469,33 +467,23 @@ mcc_status build_structure(mcc_handle* h) {
     for (int j = 0; j < c.nparam(); j++) m.red_col[j] = h->cam_col[h->intr_off[k] + j];
     if (k > 0) for (int j = 0; j < 6; j++) m.red_col[m.ext_col + j] = h->cam_col[h->ext_off[k] + j];
     m.lut_off = k * MAXC * MAXC;
-    if (c.active) { max_nb = std::max(max_nb, m.nb); max_nblk = std::max(max_nblk, m.nblk); max_cols = std::max(max_cols, m.ncols); }
+    if (c.active) { max_nb = std::max(max_nb, m.nb); max_nblk = std::max(max_nblk, m.nblk); max_red_cols = std::max(max_red_cols, 4 + c.n_dist + 7); }
   }
-  h->nt8 = max_cols <= 24 ? 3 : 4;
   for (int k = 0; k < ncam; k++) {
     const CamMeta& m = cm[k];
     for (int i = 0; i < m.ncols; i++)
       for (int j = 0; j < m.ncols; j++) {
+        const int bi = i / 3, bj = j / 3;
         int o;
-        if (h->gram_mode == 0) {
-          const int bi = i / 3, bj = j / 3;
-          if (bi <= bj) o = tri_index(bi, bj, m.nb) * 9 + (i % 3) * 3 + (j % 3);
-          else o = tri_index(bj, bi, m.nb) * 9 + (j % 3) * 3 + (i % 3);
-        } else {
-          const int bi = i / 8, bj = j / 8;
-          if (bi <= bj) o = tri_index(bi, bj, h->nt8) * 64 + (i % 8) * 8 + (j % 8);
-          else o = tri_index(bj, bi, h->nt8) * 64 + (j % 8) * 8 + (i % 8);
-        }
+        if (bi <= bj) o = tri_index(bi, bj, m.nb) * 9 + (i % 3) * 3 + (j % 3);
+        else o = tri_index(bj, bi, m.nb) * 9 + (j % 3) * 3 + (i % 3);
         lut[m.lut_off + i * MAXC + j] = o;
       }
   }
-  if (h->gram_mode == 0) {
-    h->gstride = 9 * max_nblk;
-    h->rowstride = max_nb <= 5 ? 15 : (max_nb <= 7 ? 21 : 27);   // the instantiations of k_tile_normal<RS>
-  } else {
-    h->gstride = 64 * h->nt8 * (h->nt8 + 1) / 2;
-    h->rowstride = h->nt8 == 3 ? 28 : 36;                        // k_tile_normal_mma<RS, NT8>
-  }
+  h->gstride = 9 * max_nblk;
+  // k_tile_normal<RS, MMA> works on reduced rows of (4 + n_dist) + 7 columns
+  if (h->gram_mode == 0) h->rowstride = (max_red_cols + 2) / 3 <= 5 ? 15 : 21;
+  else h->rowstride = (max_red_cols + 7) / 8 <= 2 ? 20 : 28;
 
   // reduced column -> (camera, local column)
   std::vector<int2> colmap(std::max(C, 1));
@@ -768,20 +756,16 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss) {
   const int which = h->cur;
   ST(launch_setup(h, which));
   if (h->ntiles) {
-    const size_t smem = (size_t)K1_WARPS * (64 * h->rowstride + 64) * sizeof(double);
+    const size_t smem = (size_t)K1_WARPS * (k1_rows_doubles(h->rowstride) + K1_EXTRA) * sizeof(double);
     const int grid = (h->ntiles + K1_WARPS - 1) / K1_WARPS;
     KScope ks(h, KC_TILE_NORMAL);
-#define MCC_LAUNCH_TILE_NORMAL(RS)                                                                                                          \
-    k_tile_normal<RS><<<grid, K1_WARPS * 32, smem, h->stream>>>(h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, \
-                                                                 h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p, h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p)
-#define MCC_LAUNCH_TILE_MMA(RS, NT)                                                                                                         \
-    k_tile_normal_mma<RS, NT><<<grid, K1_WARPS * 32, smem, h->stream>>>(h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, \
-                                                                         h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p, h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p)
-    if (h->gram_mode == 1) { if (h->nt8 == 3) MCC_LAUNCH_TILE_MMA(28, 3); else MCC_LAUNCH_TILE_MMA(36, 4); }
-    else if (h->rowstride == 15) MCC_LAUNCH_TILE_NORMAL(15);
-    else if (h->rowstride == 21) MCC_LAUNCH_TILE_NORMAL(21);
-    else MCC_LAUNCH_TILE_NORMAL(27);
-#undef MCC_LAUNCH_TILE_MMA
+#define MCC_LAUNCH_TILE_NORMAL(RS, MMA)                                                                                                     \
+    k_tile_normal<RS, MMA><<<grid, K1_WARPS * 32, smem, h->stream>>>(h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, \
+                                                                      h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p, h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p)
+    if (h->rowstride == 15) MCC_LAUNCH_TILE_NORMAL(15, false);
+    else if (h->rowstride == 21) MCC_LAUNCH_TILE_NORMAL(21, false);
+    else if (h->rowstride == 20) MCC_LAUNCH_TILE_NORMAL(20, true);
+    else MCC_LAUNCH_TILE_NORMAL(28, true);
 #undef MCC_LAUNCH_TILE_NORMAL
     CU(cudaGetLastError());
   }
