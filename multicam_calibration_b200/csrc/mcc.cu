@@ -281,7 +281,7 @@ struct mcc_handle {
   DBuf<int> d_gto, d_lut, d_col_param, d_fail, d_hff_tab, d_cam_tiles, d_cam_chunk0;
   DBuf<int2> d_hfc_tab;
   DBuf<CcChunk> d_cc_chunks;
-  DBuf<double> d_w_f;
+  DBuf<double> d_w_f, d_Linv, d_zf;
   int ncc_chunks = 0, cc_maxne = 1;
   DBuf<CamMeta> d_cams;
   DBuf<CcEntry> d_cc;
@@ -621,6 +621,7 @@ mcc_status build_structure(mcc_handle* h) {
   CU(up(h->d_cc_chunks, cc_chunks));
   CU(up(h->d_cam_chunk0, cam_chunk0));
   CU(h->d_w_f.reserve(std::max(h->nslots, 1)));
+  CU(h->d_Linv.reserve((size_t)std::max(h->nslots, 1) * 6)); CU(h->d_zf.reserve((size_t)std::max(h->nslots, 1) * 6));
   CU(up(h->d_tiles, tiles));
   CU(up(h->d_gto, gto));
   CU(up(h->d_col_param, h->col_param));
@@ -829,12 +830,18 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius) {
   const int C = h->C;
   CU(cudaMemsetAsync(h->d_fail.p, 0, sizeof(int), h->stream));
   {
-    const size_t smem = ((size_t)SY_FB * 6 * h->LD + SY_FB * 36 + SY_FB * 6) * sizeof(double);
+    if (h->nslots) {
+      KScope ks(h, KC_SCHUR);
+      k_frame_chol<<<(h->nslots + 127) / 128, 128, 0, h->stream>>>(h->nslots, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hff.p, h->d_gf.p, h->d_scale_f.p,
+                                                                    h->d_Lf.p, h->d_Linv.p, h->d_zf.p, h->d_fail.p);
+    }
+    CU(cudaGetLastError());
+    const size_t smem = ((size_t)SY_FB * 6 * h->LD + SY_FB * 36 + SY_FB * 12) * sizeof(double);
     dim3 grid(h->sy_gx, h->sy_gy);
     {
       KScope ks(h, KC_SCHUR);
-      k_schur_syrk<<<grid, SY_THREADS, smem, h->stream>>>(h->nslots, C, h->LD, h->npairs, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hff.p,
-                                                        h->d_gf.p, h->d_Hfc.p, h->d_scale_f.p, h->d_scale_c.p, h->d_Lf.p, h->d_S_part.p, h->d_fail.p);
+      k_schur_syrk<<<grid, SY_THREADS, smem, h->stream>>>(h->nslots, C, h->LD, h->npairs, h->d_Hfc.p, h->d_scale_f.p, h->d_scale_c.p, h->d_Lf.p, h->d_Linv.p,
+                                                          h->d_zf.p, h->d_S_part.p);
     }
     CU(cudaGetLastError());
     const int n = h->npairs * SY_T * SY_T;
@@ -1046,7 +1053,7 @@ void mcc_destroy(mcc_handle* h) {
   for (auto* b : dd) b->release();
   h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_lut.release(); h->d_col_param.release(); h->d_fail.release();
   h->d_cams.release(); h->d_cc.release(); h->d_colmap.release(); h->d_hff_tab.release(); h->d_hfc_tab.release();
-  h->d_cam_tiles.release(); h->d_cam_chunk0.release(); h->d_cc_chunks.release(); h->d_w_f.release();
+  h->d_cam_tiles.release(); h->d_cam_chunk0.release(); h->d_cc_chunks.release(); h->d_w_f.release(); h->d_Linv.release(); h->d_zf.release();
   h->world.release(); h->image.release();
   if (h->h_scal) cudaFreeHost(h->h_scal);
   if (h->h_fail) cudaFreeHost(h->h_fail);
