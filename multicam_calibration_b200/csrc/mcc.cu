@@ -288,8 +288,10 @@ struct mcc_handle {
   DBuf<int2> d_colmap;
   DBuf<double> d_camp[2], d_pose[2];   // current / candidate
   int cur = 0;
-  DBuf<double> d_setup, d_G, d_tile_s, d_Hff, d_gf, d_Hfc, d_Lf, d_cost_f, d_gmax_f, d_xn2_f, d_newcost_f, d_mcc_f, d_dx2_f, d_xn2c_f;
-  DBuf<double> d_cc_part, d_cc_sum, d_Hcc, d_gc, d_scale_c, d_scale_f, d_S_part, d_S_sum, d_M, d_yc, d_ysc, d_scal;
+  DBuf<double> d_Hff2[2], d_gf2[2], d_Hfc2[2], d_Hcc2[2], d_gc2[2];   // block sets: current point / speculative candidate
+  int blk = 0;
+  DBuf<double> d_setup, d_G, d_tile_s, d_Lf, d_cost_f, d_gmax_f, d_xn2_f, d_newcost_f, d_mcc_f, d_dx2_f, d_xn2c_f;
+  DBuf<double> d_cc_part, d_cc_sum, d_scale_c, d_scale_f, d_S_part, d_S_sum, d_M, d_yc, d_ysc, d_scal;
   double* h_scal = nullptr;            // pinned mirror of d_scal
   int* h_fail = nullptr;
   int asm_grid = 0, sy_gx = 0, sy_gy = 0;
@@ -629,11 +631,12 @@ mcc_status build_structure(mcc_handle* h) {
   CU(h->d_setup.reserve((size_t)std::max(h->ngroups, 1) * SETUP_STRIDE));
   CU(h->d_G.reserve((size_t)std::max(h->ntiles, 1) * h->gstride));
   CU(h->d_tile_s.reserve(std::max(h->ntiles, 1)));
-  CU(h->d_Hff.reserve(ns * 36)); CU(h->d_gf.reserve(ns * 6)); CU(h->d_Hfc.reserve(ns * 6 * std::max(C, 1))); CU(h->d_Lf.reserve(ns * 36));
+  for (int b = 0; b < 2; b++) { CU(h->d_Hff2[b].reserve(ns * 36)); CU(h->d_gf2[b].reserve(ns * 6)); CU(h->d_Hfc2[b].reserve(ns * 6 * std::max(C, 1))); }
+  CU(h->d_Lf.reserve(ns * 36));
   CU(h->d_cost_f.reserve(ns)); CU(h->d_gmax_f.reserve(ns)); CU(h->d_xn2_f.reserve(ns)); CU(h->d_newcost_f.reserve(ns));
   CU(h->d_mcc_f.reserve(ns)); CU(h->d_dx2_f.reserve(ns)); CU(h->d_xn2c_f.reserve(ns));
   CU(h->d_cc_part.reserve((size_t)std::max(h->ncc_chunks, 1) * h->cc_maxne)); CU(h->d_cc_sum.reserve(std::max(h->E, 1)));
-  CU(h->d_Hcc.reserve((size_t)std::max(C, 1) * std::max(C, 1))); CU(h->d_gc.reserve(std::max(C, 1)));
+  for (int b = 0; b < 2; b++) { CU(h->d_Hcc2[b].reserve((size_t)std::max(C, 1) * std::max(C, 1))); CU(h->d_gc2[b].reserve(std::max(C, 1))); }
   CU(h->d_scale_c.reserve(std::max(C, 1))); CU(h->d_scale_f.reserve(ns * 6));
   CU(h->d_S_part.reserve((size_t)h->sy_gx * h->npairs * SY_T * SY_T)); CU(h->d_S_sum.reserve((size_t)h->npairs * SY_T * SY_T));
   CU(h->d_M.reserve((size_t)(C + 1) * std::max(C, 1))); CU(h->d_yc.reserve(std::max(C, 1))); CU(h->d_ysc.reserve(std::max(C, 1)));
@@ -753,8 +756,8 @@ mcc_status allreduce(mcc_handle* h, double* p, size_t n, int op) {
 }
 
 // K1 at the current parameters: blocks, cost, gradient norm, |x|^2 -> d_scal[0..2], [8..9]
-mcc_status launch_jacobian(mcc_handle* h, int use_loss) {
-  const int which = h->cur;
+// blocks of parameter set `which` into block set `bo`
+mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo) {
   ST(launch_setup(h, which));
   if (h->ntiles) {
     const size_t smem = (size_t)K1_WARPS * (k1_rows_doubles(h->rowstride) + K1_EXTRA) * sizeof(double);
@@ -773,7 +776,7 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss) {
   if (h->nslots) {
     KScope ks(h, KC_ASSEMBLE);
     k_frame_blocks<<<h->nslots, 128, 0, h->stream>>>(h->nslots, h->ncam(), h->C, h->d_gto.p, h->d_hff_tab.p, h->d_hfc_tab.p, h->d_G.p, h->gstride,
-                                                     h->d_tile_s.p, h->d_pose[which].p, use_loss, h->d_Hff.p, h->d_gf.p, h->d_Hfc.p, h->d_cost_f.p,
+                                                     h->d_tile_s.p, h->d_pose[which].p, use_loss, h->d_Hff2[bo].p, h->d_gf2[bo].p, h->d_Hfc2[bo].p, h->d_cost_f.p,
                                                      h->d_gmax_f.p, h->d_xn2_f.p, h->d_w_f.p);
   }
   CU(cudaGetLastError());
@@ -809,7 +812,7 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss) {
   }
   {
     KScope ks(h, KC_REDUCE);
-    k_scatter_cc<<<1, 1024, 0, h->stream>>>(h->C, h->E, h->d_cc.p, h->d_cc_sum.p, h->d_col_param.p, h->d_camp[which].p, h->d_Hcc.p, h->d_gc.p, h->d_scal.p + 8);
+    k_scatter_cc<<<1, 1024, 0, h->stream>>>(h->C, h->E, h->d_cc.p, h->d_cc_sum.p, h->d_col_param.p, h->d_camp[which].p, h->d_Hcc2[bo].p, h->d_gc2[bo].p, h->d_scal.p + 8);
   }
   CU(cudaGetLastError());
   return MCC_OK;
@@ -825,14 +828,17 @@ mcc_status read_scalars(mcc_handle* h) {
 }
 
 // K2..K5 for one trust-region radius: candidate parameters in the other buffer, scalars in d_scal[3..6], [10..12]
-mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius) {
+// K2..K4 for one trust-region radius, then the evaluation of the candidate: either the cheap residual-only pass
+// (speculate = false) or straight away the full Jacobian pass into the OTHER block set (speculate = true), whose
+// cost doubles as the candidate cost; an accepted step then needs no further pass.
+mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool speculate) {
   const int cur = h->cur, cand = 1 - cur;
   const int C = h->C;
   CU(cudaMemsetAsync(h->d_fail.p, 0, sizeof(int), h->stream));
   {
     if (h->nslots) {
       KScope ks(h, KC_SCHUR);
-      k_frame_chol<<<(h->nslots + 127) / 128, 128, 0, h->stream>>>(h->nslots, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hff.p, h->d_gf.p, h->d_scale_f.p,
+      k_frame_chol<<<(h->nslots + 127) / 128, 128, 0, h->stream>>>(h->nslots, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hff2[h->blk].p, h->d_gf2[h->blk].p, h->d_scale_f.p,
                                                                     h->d_Lf.p, h->d_Linv.p, h->d_zf.p, h->d_fail.p);
     }
     CU(cudaGetLastError());
@@ -840,7 +846,7 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius) {
     dim3 grid(h->sy_gx, h->sy_gy);
     {
       KScope ks(h, KC_SCHUR);
-      k_schur_syrk<<<grid, SY_THREADS, smem, h->stream>>>(h->nslots, C, h->LD, h->npairs, h->d_Hfc.p, h->d_scale_f.p, h->d_scale_c.p, h->d_Lf.p, h->d_Linv.p,
+      k_schur_syrk<<<grid, SY_THREADS, smem, h->stream>>>(h->nslots, C, h->LD, h->npairs, h->d_Hfc2[h->blk].p, h->d_scale_f.p, h->d_scale_c.p, h->d_Lf.p, h->d_Linv.p,
                                                           h->d_zf.p, h->d_S_part.p);
     }
     CU(cudaGetLastError());
@@ -858,11 +864,11 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius) {
     {
       KScope ks(h, KC_SOLVE);
       if (packed)
-        k_solve_cam<true><<<1, CH_THREADS, need, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc.p, h->d_gc.p, h->d_S_sum.p,
+        k_solve_cam<true><<<1, CH_THREADS, need, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc2[h->blk].p, h->d_gc2[h->blk].p, h->d_S_sum.p,
                                                               h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
                                                               h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, h->d_fail.p);
       else
-        k_solve_cam<false><<<1, CH_THREADS, 0, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc.p, h->d_gc.p, h->d_S_sum.p,
+        k_solve_cam<false><<<1, CH_THREADS, 0, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc2[h->blk].p, h->d_gc2[h->blk].p, h->d_S_sum.p,
                                                             h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
                                                             h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, h->d_fail.p);
     }
@@ -871,15 +877,16 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius) {
   if (h->nslots) {
     {
       KScope ks(h, KC_BACKSUB);
-      k_backsub<<<(h->nslots + 3) / 4, 128, 0, h->stream>>>(h->nslots, C, h->d_Hff.p, h->d_gf.p, h->d_Hfc.p, h->d_Lf.p, h->d_scale_f.p, h->d_ysc.p,
+      k_backsub<<<(h->nslots + 3) / 4, 128, 0, h->stream>>>(h->nslots, C, h->d_Hff2[h->blk].p, h->d_gf2[h->blk].p, h->d_Hfc2[h->blk].p, h->d_Lf.p, h->d_scale_f.p, h->d_ysc.p,
                                                          h->d_pose[cur].p, h->d_pose[cand].p, h->d_mcc_f.p, h->d_dx2_f.p, h->d_xn2c_f.p, h->d_fail.p);
     }
     CU(cudaGetLastError());
   }
-  ST(launch_cost(h, cand, o.use_loss, h->d_newcost_f.p, nullptr));
+  if (speculate) ST(launch_jacobian(h, o.use_loss, cand, 1 - h->blk));   // cost, |x|^2, gradient norm -> d_scal[0..2], [8..9]
+  else ST(launch_cost(h, cand, o.use_loss, h->d_newcost_f.p, nullptr));
   ReduceJobs jobs;
   std::memset(&jobs, 0, sizeof(jobs));
-  jobs.j[0] = ReduceJob{h->d_newcost_f.p, 0};
+  jobs.j[0] = ReduceJob{speculate ? h->d_cost_f.p : h->d_newcost_f.p, 0};
   jobs.j[1] = ReduceJob{h->d_mcc_f.p, 0};
   jobs.j[2] = ReduceJob{h->d_dx2_f.p, 0};
   jobs.j[3] = ReduceJob{h->d_xn2c_f.p, 0};
@@ -917,10 +924,11 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
     S.num_iterations++;
   };
   double t0 = now_s();
-  ST(launch_jacobian(h, o.use_loss));
+  ST(launch_jacobian(h, o.use_loss, h->cur, h->blk));
   {
     KScope ks(h, KC_OTHER);
-    k_jacobi_scale<<<(std::max(h->C, h->nslots * 6) + 127) / 128, 128, 0, h->stream>>>(h->nslots, h->C, o.jacobi_scaling, h->d_Hcc.p, h->d_Hff.p, h->d_scale_c.p, h->d_scale_f.p);
+    k_jacobi_scale<<<(std::max(h->C, h->nslots * 6) + 127) / 128, 128, 0, h->stream>>>(h->nslots, h->C, o.jacobi_scaling, h->d_Hcc2[h->blk].p, h->d_Hff2[h->blk].p,
+                                                                                       h->d_scale_c.p, h->d_scale_f.p);
   }
   CU(cudaGetLastError());
   ST(read_scalars(h));
@@ -937,35 +945,23 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
     return MCC_OK;
   };
   if (gmax <= o.gradient_tolerance) return finish(0, 0, gmax);
-  // After an accepted step the Jacobian pass at the new point is only ENQUEUED; its scalars (cost, gradient norm)
-  // are read together with the next step's, so an iteration costs one host synchronisation.  If the gradient
-  // tolerance turns out to be met, the speculative step is simply dropped.
-  bool pending = false;
-  double p_cost_change = 0, p_step_norm = 0, p_ratio = 0;
-  auto absorb_pending = [&]() {
-    cost = h->h_scal[0];
-    gmax = std::max(h->h_scal[2], h->h_scal[8]);
-    S.num_successful++;
-    log_row(cost, p_cost_change, gmax, p_step_norm, p_ratio, radius);
-    pending = false;
-  };
+  // Candidate evaluation is speculative while steps are being accepted: the full Jacobian pass at x+ goes into the
+  // spare block set and its cost is the candidate cost, so an accepted iteration is ONE pass over the observations
+  // and ONE host synchronisation.  After a rejected or invalid step the next candidate gets the cheap cost-only
+  // pass first (Ceres' order), and the Jacobian pass follows only on acceptance.
+  bool speculate = true;
   int invalid_run = 0, iter = 0;
   while (true) {
-    if (iter >= o.max_num_iterations) {
-      if (pending) { ST(read_scalars(h)); absorb_pending(); if (gmax <= o.gradient_tolerance) return finish(0, 0, gmax); }
-      return finish(1, 3, iter);
-    }
+    if (iter >= o.max_num_iterations) return finish(1, 3, iter);
     iter++;
     t0 = now_s();
-    ST(launch_step(h, o, radius));
+    const bool spec = speculate;
+    ST(launch_step(h, o, radius, spec));
     ST(read_scalars(h));
-    S.t_linear += now_s() - t0; S.n_linear_solves++; S.n_residual_evals++;
-    if (pending) {
-      absorb_pending();
-      if (gmax <= o.gradient_tolerance) return finish(0, 0, gmax);
-    }
+    S.t_linear += now_s() - t0; S.n_linear_solves++;
+    if (spec) S.n_jacobian_evals++; else S.n_residual_evals++;
     const int flags = *h->h_fail;
-    const double new_cost = h->h_scal[3];
+    const double new_cost = spec ? h->h_scal[0] : h->h_scal[3];
     const double mcc = h->h_scal[4] + h->h_scal[10];
     const double step_norm = std::sqrt(h->h_scal[5] + h->h_scal[11]);
     const double xn_cand = std::sqrt(h->h_scal[6] + h->h_scal[12]);
@@ -975,6 +971,7 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
       if (invalid_run >= o.max_num_consecutive_invalid_steps) return finish(2, 4, invalid_run);
       radius /= decrease_factor; decrease_factor *= 2.0;
       S.num_unsuccessful++;
+      speculate = false;
       log_row(cost, 0, gmax, 0, 0, radius);
       if (radius < o.min_trust_region_radius) return finish(0, 5, radius);
       continue;
@@ -990,19 +987,29 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
       radius = radius / std::max(1.0 / 3.0, 1.0 - std::pow(2.0 * ratio - 1.0, 3));
       radius = std::min(o.max_trust_region_radius, radius);
       decrease_factor = 2.0;
-      ST(launch_jacobian(h, o.use_loss));
-      S.n_jacobian_evals++;
-      pending = true;
-      p_cost_change = cost_change; p_step_norm = step_norm; p_ratio = ratio;
+      if (spec) {
+        h->blk = 1 - h->blk;                 // the candidate's blocks are already there
+        cost = new_cost;
+        gmax = std::max(h->h_scal[2], h->h_scal[8]);
+      } else {
+        t0 = now_s();
+        ST(launch_jacobian(h, o.use_loss, h->cur, h->blk));
+        ST(read_scalars(h));
+        S.t_jacobian += now_s() - t0; S.n_jacobian_evals++;
+        cost = h->h_scal[0];
+        gmax = std::max(h->h_scal[2], h->h_scal[8]);
+      }
+      speculate = true;
+      S.num_successful++;
+      log_row(cost, cost_change, gmax, step_norm, ratio, radius);
+      if (gmax <= o.gradient_tolerance) return finish(0, 0, gmax);
     } else {
       radius /= decrease_factor; decrease_factor *= 2.0;
       S.num_unsuccessful++;
+      speculate = false;
       log_row(cost, cost_change, 0.0, step_norm, ratio, radius);
     }
-    if (radius < o.min_trust_region_radius) {
-      if (pending) { ST(read_scalars(h)); absorb_pending(); }
-      return finish(0, 5, radius);
-    }
+    if (radius < o.min_trust_region_radius) return finish(0, 5, radius);
   }
 }
 
@@ -1047,8 +1054,8 @@ void mcc_destroy(mcc_handle* h) {
   if (h->device >= 0) cudaSetDevice(h->device);
   if (h->comm && nccl().CommDestroy) nccl().CommDestroy(h->comm);
   DBuf<double>* dd[] = {&h->d_aos_w, &h->d_aos_i, &h->d_X, &h->d_Y, &h->d_Z, &h->d_U, &h->d_V, &h->d_res, &h->d_camp[0], &h->d_camp[1], &h->d_pose[0], &h->d_pose[1],
-                        &h->d_setup, &h->d_G, &h->d_tile_s, &h->d_Hff, &h->d_gf, &h->d_Hfc, &h->d_Lf, &h->d_cost_f, &h->d_gmax_f, &h->d_xn2_f, &h->d_newcost_f,
-                        &h->d_mcc_f, &h->d_dx2_f, &h->d_xn2c_f, &h->d_cc_part, &h->d_cc_sum, &h->d_Hcc, &h->d_gc, &h->d_scale_c, &h->d_scale_f, &h->d_S_part,
+                        &h->d_setup, &h->d_G, &h->d_tile_s, &h->d_Hff2[0], &h->d_Hff2[1], &h->d_gf2[0], &h->d_gf2[1], &h->d_Hfc2[0], &h->d_Hfc2[1], &h->d_Lf, &h->d_cost_f, &h->d_gmax_f, &h->d_xn2_f, &h->d_newcost_f,
+                        &h->d_mcc_f, &h->d_dx2_f, &h->d_xn2c_f, &h->d_cc_part, &h->d_cc_sum, &h->d_Hcc2[0], &h->d_Hcc2[1], &h->d_gc2[0], &h->d_gc2[1], &h->d_scale_c, &h->d_scale_f, &h->d_S_part,
                         &h->d_S_sum, &h->d_M, &h->d_yc, &h->d_ysc, &h->d_scal};
   for (auto* b : dd) b->release();
   h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_lut.release(); h->d_col_param.release(); h->d_fail.release();
@@ -1407,15 +1414,15 @@ long long mcc_num_active_frames(const mcc_handle* h) { return h ? h->nslots : 0;
 mcc_status mcc_eval_normal_blocks(mcc_handle* h, int use_loss, double* cost, double* Hcc, double* gc, double* Hff, double* gf, double* Hfc, int* frame_ids) {
   if (!h) return MCC_ERR_BAD_ARG;
   ST(prepare(h));
-  ST(launch_jacobian(h, use_loss));
+  ST(launch_jacobian(h, use_loss, h->cur, h->blk));
   ST(read_scalars(h));
   if (cost) *cost = h->h_scal[0];
   const size_t C = h->C, ns = h->nslots;
-  if (Hcc && C) CU(cudaMemcpyAsync(Hcc, h->d_Hcc.p, C * C * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-  if (gc && C) CU(cudaMemcpyAsync(gc, h->d_gc.p, C * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-  if (Hff && ns) CU(cudaMemcpyAsync(Hff, h->d_Hff.p, ns * 36 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-  if (gf && ns) CU(cudaMemcpyAsync(gf, h->d_gf.p, ns * 6 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-  if (Hfc && ns && C) CU(cudaMemcpyAsync(Hfc, h->d_Hfc.p, ns * 6 * C * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  if (Hcc && C) CU(cudaMemcpyAsync(Hcc, h->d_Hcc2[h->blk].p, C * C * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  if (gc && C) CU(cudaMemcpyAsync(gc, h->d_gc2[h->blk].p, C * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  if (Hff && ns) CU(cudaMemcpyAsync(Hff, h->d_Hff2[h->blk].p, ns * 36 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  if (gf && ns) CU(cudaMemcpyAsync(gf, h->d_gf2[h->blk].p, ns * 6 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  if (Hfc && ns && C) CU(cudaMemcpyAsync(Hfc, h->d_Hfc2[h->blk].p, ns * 6 * C * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaStreamSynchronize(h->stream));
   if (frame_ids) for (size_t s = 0; s < ns; s++) frame_ids[s] = h->slot_frame[s];
   return MCC_OK;
