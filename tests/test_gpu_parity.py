@@ -286,3 +286,47 @@ def test_pinned_and_pageable_inputs_agree(small_rig, c3_rig):
     s2 = cal.runCalibration()
     assert s2.final_cost == s0.final_cost and np.array_equal(cal.getParams(), ref.getParams())
     cal.close(); ref.close()
+
+
+def test_full_size_c4_properties(built):
+    """config c4 at BASELINE.json's full size (8 cameras, 10 000 frames, ~20 M residuals, 60 106 parameters): too big
+    for the oracle in a test, so size-independent properties are checked instead"""
+    from multicam_calibration_b200 import capi, synth
+    rig = synth.config_c4()
+    assert rig.num_cam_params == 106 and rig.num_cam_params + 6 * rig.num_frames == 60106
+    cal = capi.calibrator_from_rig(rig, device=0)
+    s = cal.runCalibration()
+    assert s.termination == 0 and s.num_residuals == 2 * rig.num_obs
+    tr = s.trace()
+    # accepted rows: strictly decreasing cost; gradient drops by orders of magnitude
+    acc = tr["cost"][np.concatenate([[True], tr["ratio"][1:] > 1e-3])]
+    assert np.all(np.diff(acc) < 0)
+    assert tr["gradient_max"][-1] < 1e-4 * tr["gradient_max"][0]
+    p = cal.getParams()
+    # (1) the cost the solver reports is the cost of the parameters it returns, by two independent device paths:
+    #     the Jacobian pass (summary) and the residual-only pass (mcc_eval_cost)
+    c_eval = cal.evalCost(use_loss=True)
+    assert abs(c_eval - s.final_cost) <= 1e-12 * s.final_cost
+    # (2) ... and by the residuals themselves, Huber applied per frame on the host (checksum of checksums)
+    r = cal.testCalibration()
+    e2 = r[:, 0] ** 2 + r[:, 1] ** 2
+    per_frame = np.add.reduceat(e2, np.concatenate([[0], np.cumsum(rig.npts.sum(axis=1))[:-1]]))
+    rho = np.where(per_frame > 1.0, 2.0 * np.sqrt(per_frame) - 1.0, per_frame)
+    assert abs(0.5 * rho.sum() - s.final_cost) <= 1e-11 * s.final_cost
+    # (3) idempotence: solving again from the initial values gives the same bits
+    s2 = cal.runCalibration()
+    assert s2.final_cost == s.final_cost and s2.num_iterations == s.num_iterations
+    assert np.array_equal(cal.getParams(), p)
+    # (4) restarting from the solution: nothing left to gain (a handful of noise-floor iterations at most)
+    opt = capi.default_options()
+    opt.keep_params = 1
+    s3 = cal.runCalibration(opt)
+    assert s3.num_iterations <= 4 and abs(s3.final_cost - s.final_cost) <= 1e-10 * s.final_cost
+    # (5) the generating cameras are recovered (noise 0.2 px, 10 M corners)
+    res = cal.getCalibrationResults()
+    for k, c in enumerate(rig.truth["cameras"]):
+        np.testing.assert_allclose(res[k].intrinsics, c.intrinsics, rtol=2e-4)
+        np.testing.assert_allclose(res[k].distortion_coeffs, c.distortion_coeffs, atol=2e-3)
+        if k > 0:
+            np.testing.assert_allclose(res[k].T_cn_cnm1[:3, 3], c.T_cn_cnm1[:3, 3], atol=2e-4)
+    cal.close()
