@@ -219,6 +219,13 @@ mcc_status mcc_reprojection_cost_noalloc(int model, int n_dist, const double* d_
                                          const double* d_V, const uint8_t* d_mask, double* d_sum_sq, void* stream,
                                          char* errbuf, size_t errbuf_len);
 
+/* get_init_pose::get_init_pose (/root/reference/src/get_init_pose.cpp:81-140): initial pose T_cam_world of ONE
+ * camera view from the homography between the board plane (world x, y; z ignored) and the undistorted image points,
+ * decomposed as in decomposeHomography (:46-75).  Host code (an O(N) one-off before the solve).  Needs >= 4 points
+ * (MCC_ERR_NO_DATA otherwise); MCC_ERR_NUMERICAL for degenerate configurations. */
+mcc_status mcc_init_pose(int model, const double* intr, int n_dist, const double* dist, int npts, const double* world_xyz,
+                         const double* image_uv, double* T_cam_world);
+
 /* Transform helpers used by the facade: Eigen AngleAxisd(R) route of transform_to_rvec_tvec
  * (calibrator.cpp:157-170) and utils::rotation_matrix (utils.h:29-39). */
 void mcc_transform_to_rvec_tvec(const double T[16], double out6[6]);

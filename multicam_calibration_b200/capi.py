@@ -72,7 +72,7 @@ SYMBOLS = ["mcc_version", "mcc_default_options", "mcc_summary_size", "mcc_create
            "mcc_set_mask", "mcc_num_reduced_cam_cols", "mcc_num_active_frames", "mcc_eval_normal_blocks", "mcc_comm_unique_id", "mcc_comm_init",
            "mcc_transform_to_rvec_tvec", "mcc_rvec_tvec_to_transform", "mcc_timer_start", "mcc_timer_stop", "mcc_set_kernel_timing",
            "mcc_num_kernel_classes", "mcc_kernel_class_name", "mcc_get_kernel_times", "mcc_measure_fp64_peak",
-           "mcc_reprojection_cost_noalloc", "mcc_set_gram_mode", "mcc_get_gram_mode"]
+           "mcc_reprojection_cost_noalloc", "mcc_set_gram_mode", "mcc_get_gram_mode", "mcc_init_pose"]
 
 
 def build(force: bool = False) -> str:
@@ -140,6 +140,7 @@ def lib():
     L.mcc_kernel_class_name.restype = C.c_char_p
     L.mcc_get_kernel_times.argtypes = [vp, dp, C.POINTER(C.c_longlong), C.c_int]
     L.mcc_measure_fp64_peak.argtypes = [C.c_int, dp]
+    L.mcc_init_pose.argtypes = [C.c_int, dp, C.c_int, dp, C.c_int, dp, dp, dp]
     L.mcc_set_gram_mode.argtypes = [vp, C.c_int]
     L.mcc_get_gram_mode.argtypes = [vp]
     L.mcc_reprojection_cost_noalloc.argtypes = [C.c_int, C.c_int] + [vp, vp, C.c_size_t] + [vp] * 8 + [C.c_char_p, C.c_size_t]
@@ -191,6 +192,19 @@ def reprojection_cost_noalloc(model: int, n_dist: int, d_intr: int, d_Rt: int, n
                                              stream, err, len(err))
     if st != 0:
         raise MccError(st, err.value.decode())
+
+
+def init_pose(camera: Camera, world_xyz: np.ndarray, image_uv: np.ndarray) -> np.ndarray:
+    """get_init_pose (/root/reference/src/get_init_pose.cpp:81-140): 4x4 T_cam_world of one camera view"""
+    w = np.ascontiguousarray(world_xyz, dtype=np.float64).reshape(-1, 3)
+    im = np.ascontiguousarray(image_uv, dtype=np.float64).reshape(-1, 2)
+    intr = np.ascontiguousarray(camera.intrinsics, dtype=np.float64)
+    dist = np.ascontiguousarray(camera.distortion_coeffs, dtype=np.float64)
+    T = np.zeros(16)
+    st = lib().mcc_init_pose(camera.model_id, _dp(intr), len(dist), _dp(dist), len(w), _dp(w), _dp(im), _dp(T))
+    if st != 0:
+        raise MccError(st, "mcc_init_pose failed")
+    return T.reshape(4, 4)
 
 
 def transform_to_rvec_tvec(T) -> np.ndarray:

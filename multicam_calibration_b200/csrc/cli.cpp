@@ -6,9 +6,10 @@
 // again, :202-207), write the result YAML to a file and to stdout (:413-453), feed the results back as the
 // cameras (updateCameras, :455-469) and print the reprojection report with per-camera residual dumps (:292-345).
 //
-// Initial poses: the reference derives them with OpenCV (get_init_pose.cpp, a "next" item in SURVEY.md section 8f);
-// here they are read from --init-poses: one line per frame rank, 16 numbers (row-major 4x4 T_c0_w).  Frames
-// without a pose line or with "nan" are skipped like frames where the reference finds no detections (:638-641).
+// Initial poses: computed per frame like the reference's guessCameraPose (:510-543, homography of the first camera
+// that saw the board, get_init_pose.h), or -- with --init-poses -- read from a file: one line per frame rank,
+// 16 numbers (row-major 4x4 T_c0_w); frames without a pose line or with "nan" are skipped like frames where the
+// reference finds no detections (:638-641).
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -22,13 +23,14 @@
 
 #include "multicam_calibration/calibrator.h"
 #include "multicam_calibration/corners_csv.h"
+#include "multicam_calibration/get_init_pose.h"
 #include "multicam_calibration/kalibr_yaml.h"
 
 using namespace multicam_calibration;
 
 static void usage() {
   std::fprintf(stderr,
-               "usage: mcc_calibrate --calib initial.yaml --corners corners.csv --init-poses poses.txt [--output out.yaml]\n"
+               "usage: mcc_calibrate --calib initial.yaml --corners corners.csv [--init-poses poses.txt] [--output out.yaml]\n"
                "                     [--outlier-pixel-threshold px] [--fix-intrinsics] [--device n] [--residuals-dir dir] [--quiet]\n");
 }
 
@@ -93,7 +95,7 @@ int main(int argc, char **argv) {
     else if (a == "--quiet") quiet = true;
     else { usage(); return 2; }
   }
-  if (calib.empty() || corners.empty() || poses_file.empty()) { usage(); return 2; }
+  if (calib.empty() || corners.empty()) { usage(); return 2; }
 
   CameraExtrinsics T_imu_body;
   CalibDataVec cameras;
@@ -123,7 +125,7 @@ int main(int argc, char **argv) {
   // initial poses
   std::vector<CameraExtrinsics> poses(nframes);
   std::vector<bool> have(nframes, false);
-  {
+  if (!poses_file.empty()) {
     std::ifstream in(poses_file);
     if (!in.is_open()) { std::fprintf(stderr, "cannot open %s\n", poses_file.c_str()); return 1; }
     std::string line;
@@ -142,6 +144,7 @@ int main(int argc, char **argv) {
     CamWorldPoints wp; CamImagePoints ip;
     bool any = false;
     for (size_t k = 0; k < cameras.size(); k++) { wp.push_back(worldPoints[k][f]); ip.push_back(imagePoints[k][f]); any = any || !wp.back().empty(); }
+    if (any && poses_file.empty()) have[f] = guessCameraPose(cameras, wp, ip, &poses[f], (int)f);
     if (!any || !have[f]) { std::printf("no detections found, skipping frame %zu\n", f); continue; }
     cal.addPoints((int)f, wp, ip, poses[f]);
     frame_of_added.push_back(f);

@@ -37,6 +37,24 @@ def _write_kat_inputs(model, tmp_path):
 
 
 @pytest.mark.gpu
+def test_cli_radtan_fixture_with_own_initial_poses(built, tmp_path):
+    """same flow, but the initial poses come from the library's own homography step (guessCameraPose,
+    calibration_nodelet.cpp:510-543) instead of a file: the solve lands on the reference's logged result"""
+    _write_kat_inputs("radtan", tmp_path)
+    out_yaml = tmp_path / "radtan-out.yaml"
+    r = subprocess.run([os.path.join(PKG, "mcc_calibrate"), "--calib", str(tmp_path / "initial.yaml"), "--corners", str(tmp_path / "corners.csv"),
+                        "--output", str(out_yaml)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    so = r.stdout
+    assert "read 900 frames from" in so and "Num params: 5412" in so and "Num residuals: 715662" in so
+    assert "Parameter tolerance reached" in so
+    y = open(out_yaml).read()
+    assert "  intrinsics: [151, 152, 173, 144]\n" in y
+    assert "  distortion_coeffs: [0.155003, -0.180002, -0.005, -0.000300001, 0.0440008, 0.00500274, 0.00399778, -0.000399239]\n" in y
+    assert "max error: 2.37361e-05 px at frame: 84 for cam: 0" in so
+
+
+@pytest.mark.gpu
 def test_cli_radtan_fixture_matches_reference_log(built, tmp_path):
     """the reference's `roslaunch test_calib.launch type:=radtan` flow, headless: same console facts and YAML as
     /root/reference/test/radtan/correct_output.txt"""
