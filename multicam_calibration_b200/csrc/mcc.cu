@@ -395,7 +395,7 @@ mcc_status ensure_device(mcc_handle* h) {
     CU((cudaFuncSetAttribute(k_tile_normal<20, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
     CU((cudaFuncSetAttribute(k_tile_normal<28, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
     CU(cudaFuncSetAttribute(k_schur_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    CU(cudaFuncSetAttribute(k_solve_cam<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(k_solve_cam<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 196 * 1024));
     h->attrs_set = true;
   }
   return MCC_OK;
@@ -789,7 +789,9 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo) {
     CU(cudaGetLastError());
     {
       KScope ks(h, KC_REDUCE);
-      k_cc_reduce<<<(h->E + 127) / 128, 128, 0, h->stream>>>(h->E, h->d_cc.p, h->d_cam_chunk0.p, h->d_cc_chunks.p, h->cc_maxne, h->d_cc_part.p, h->d_cc_sum.p);
+      CU(cudaMemsetAsync(h->d_cc_sum.p, 0, (size_t)h->E * sizeof(double), h->stream));
+      k_cc_reduce<<<h->ncam(), 1024, (size_t)CCR_S * h->cc_maxne * sizeof(double), h->stream>>>(h->ncam(), h->d_cam_chunk0.p, h->d_cc_chunks.p, h->cc_maxne,
+                                                                                               h->d_cc_part.p, h->d_cc_sum.p);
     }
     CU(cudaGetLastError());
   }
@@ -853,14 +855,14 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     const int n = h->npairs * SY_T * SY_T;
     {
       KScope ks(h, KC_REDUCE);
-      k_reduce_rows<<<(n + 127) / 128, 128, 0, h->stream>>>(h->sy_gx, n, h->d_S_part.p, h->d_S_sum.p);
+      k_reduce_rows<<<(n + RR_E - 1) / RR_E, RR_E * RR_S, 0, h->stream>>>(h->sy_gx, n, h->d_S_part.p, h->d_S_sum.p);
     }
     CU(cudaGetLastError());
     ST(allreduce(h, h->d_S_sum.p, n, ncclSum_));
   }
   {
     const size_t need = ((size_t)C * (C + 1) / 2 + C + 1) * sizeof(double);   // packed lower triangle + rhs row
-    const bool packed = need <= 200 * 1024;
+    const bool packed = need <= 196 * 1024;   // + ~30 KB of static shared memory in k_solve_cam
     {
       KScope ks(h, KC_SOLVE);
       if (packed)
