@@ -469,6 +469,27 @@ mcc_status build_structure(mcc_handle* h) {
     for (int j = 0; j < c.nparam(); j++) m.red_col[j] = h->cam_col[h->intr_off[k] + j];
     if (k > 0) for (int j = 0; j < 6; j++) m.red_col[m.ext_col + j] = h->cam_col[h->ext_off[k] + j];
     m.lut_off = k * MAXC * MAXC;
+    {
+      // contraction units of the reduced (n_k + 7)-column Gram matrix: walk the block columns, pair up the still
+      // uncovered block pairs that share the column; an odd one out is left to its other column
+      const int rnb = (4 + c.n_dist + 7 + 2) / 3;
+      bool used[9][9];
+      for (int a = 0; a < 9; a++) for (int b = 0; b < 9; b++) used[a][b] = false;
+      m.nunits = 0;
+      for (int sidx = 0; sidx < rnb; sidx++) {
+        std::vector<int> partners;
+        for (int q = 0; q < rnb; q++) if (!used[std::min(sidx, q)][std::max(sidx, q)]) partners.push_back(q);
+        // keep the partner with the highest index for later if the count is odd and that column still has open pairs
+        if (partners.size() % 2 == 1 && partners.back() > sidx) partners.pop_back();
+        for (size_t q = 0; q < partners.size(); q += 2) {
+          const int o1 = partners[q], o2 = q + 1 < partners.size() ? partners[q + 1] : -1;
+          m.unit_s[m.nunits] = (int8_t)sidx; m.unit_o1[m.nunits] = (int8_t)o1; m.unit_o2[m.nunits] = (int8_t)o2;
+          m.nunits++;
+          used[std::min(sidx, o1)][std::max(sidx, o1)] = true;
+          if (o2 >= 0) used[std::min(sidx, o2)][std::max(sidx, o2)] = true;
+        }
+      }
+    }
     if (c.active) { max_nb = std::max(max_nb, m.nb); max_nblk = std::max(max_nblk, m.nblk); max_red_cols = std::max(max_red_cols, 4 + c.n_dist + 7); }
   }
   for (int k = 0; k < ncam; k++) {
