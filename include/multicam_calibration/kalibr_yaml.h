@@ -7,8 +7,8 @@
 //      back to the default, :133-141), fix_intrinsics, fix_extrinsics, active, flip_code, rotate_code; top-level
 //      T_imu_body.  cam0's T_cn_cnm1 is forced to identity (:171-175); an exact-identity rotation for cam>0 is
 //      replaced by a 1e-5 rad rotation about x (:176-183) because the rotation Jacobian vanishes at identity.
-// Out: writeCalibration (:413-453) with print_tf (:360-371) and vec2str (:347-358) formatting.  The stereo
-//      rectification_matrix / projection_matrix entries (compute_RPQ, OpenCV) are not produced.
+// Out: writeCalibration (:413-453) with print_tf (:360-371) and vec2str (:347-358) formatting, including the stereo
+//      rectification_matrix / projection_matrix entries of cameras 0 and 1 (compute_RPQ, stereo_rectify.h).
 //
 // The parser handles the YAML subset these files use: nested block mappings by indentation, scalars, flow
 // sequences "[a, b]" and block sequences of flow sequences ("- [a, b, c, d]").
@@ -26,6 +26,7 @@
 #include <vector>
 
 #include "multicam_calibration/calibration_data.h"
+#include "multicam_calibration/stereo_rectify.h"
 
 namespace multicam_calibration {
 namespace yaml_detail {
@@ -212,6 +213,19 @@ inline void print_tf(std::ostream &os, const std::string &p, const CameraExtrins
   os.flags(f);
   os.precision(prec);
 }
+// the same for the 3x3 / 3x4 rectification matrices (row-major arrays)
+inline void print_mat(std::ostream &os, const std::string &p, const double *m, int rows, int cols) {
+  std::ios::fmtflags f(os.flags());
+  const std::streamsize prec = os.precision();
+  os << std::fixed << std::setprecision(11);
+  for (int i = 0; i < rows; i++) {
+    os << p << "- [";
+    for (int j = 0; j < cols - 1; j++) os << std::setw(14) << m[i * cols + j] << ", ";
+    os << std::setw(14) << m[i * cols + cols - 1] << "] " << std::endl;
+  }
+  os.flags(f);
+  os.precision(prec);
+}
 // vec2str (calibration_nodelet.cpp:347-358): default ostream formatting, 6 significant digits
 inline std::string vec2str(const std::vector<double> &v) {
   std::stringstream ss;
@@ -220,13 +234,22 @@ inline std::string vec2str(const std::vector<double> &v) {
   ss << "]";
   return ss.str();
 }
-// writeCalibration (calibration_nodelet.cpp:413-453), without the OpenCV stereo rectification block
+// writeCalibration (calibration_nodelet.cpp:413-453)
 inline void write_calibration(std::ostream &os, const CalibDataVec &results, const CameraExtrinsics &T_imu_body = zeros()) {
+  Rectification rp;
+  bool hasRP = false;
+  try { hasRP = compute_RPQ(0, 1, results, &rp); } catch (...) { hasRP = false; }
   for (size_t k = 0; k < results.size(); k++) {
     const CalibrationData &cd = results[k];
     os << cd.name << ":" << std::endl;
     if (isNonZero(cd.T_cam_imu)) { os << "  T_cam_imu:" << std::endl; print_tf(os, "  ", cd.T_cam_imu); }
     if (k > 0) { os << "  T_cn_cnm1:" << std::endl; print_tf(os, "  ", cd.T_cn_cnm1); }
+    if (hasRP && k < 2) {
+      os << "  rectification_matrix:" << std::endl;
+      print_mat(os, "  ", rp.R[k], 3, 3);
+      os << "  projection_matrix:" << std::endl;
+      print_mat(os, "  ", rp.P[k], 3, 4);
+    }
     const CameraIntrinsics &ci = cd.intrinsics;
     os << "  camera_model: " << ci.camera_model << std::endl;
     os << "  intrinsics: " << vec2str(ci.intrinsics) << std::endl;

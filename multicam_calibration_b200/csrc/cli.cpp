@@ -31,7 +31,8 @@ using namespace multicam_calibration;
 static void usage() {
   std::fprintf(stderr,
                "usage: mcc_calibrate --calib initial.yaml --corners corners.csv [--init-poses poses.txt] [--output out.yaml]\n"
-               "                     [--outlier-pixel-threshold px] [--fix-intrinsics] [--device n] [--residuals-dir dir] [--quiet]\n");
+               "                     [--outlier-pixel-threshold px] [--fix-intrinsics] [--device n] [--residuals-dir dir]\n"
+               "                     [--latest-link name.yaml] [--quiet]\n");
 }
 
 // calibration_nodelet.cpp:292-345
@@ -77,7 +78,7 @@ static std::string reprojection_report(Calibrator &cal, const CalibDataVec &cali
 }
 
 int main(int argc, char **argv) {
-  std::string calib, corners, poses_file, output, residuals_dir;
+  std::string calib, corners, poses_file, output, residuals_dir, latest_link;
   double outlier = -1.0;
   bool fix_intr = false, quiet = false;
   int device = -1;
@@ -92,6 +93,7 @@ int main(int argc, char **argv) {
     else if (a == "--fix-intrinsics") fix_intr = true;
     else if (a == "--device") device = std::atoi(next().c_str());
     else if (a == "--residuals-dir") residuals_dir = next();
+    else if (a == "--latest-link") latest_link = next();
     else if (a == "--quiet") quiet = true;
     else { usage(); return 2; }
   }
@@ -182,6 +184,11 @@ int main(int argc, char **argv) {
   }
   cal.setCameras(cameras);   // (:227) params_ of the finished run stay in place for the test below
   write_calibration(std::cout, results, T_imu_body);
+  if (!latest_link.empty()) {
+    // "ln -sf <file> <calib_dir>/<latest_link_name>" (calibration_nodelet.cpp:232-235)
+    const std::string cmd = "ln -sf " + output + " " + latest_link;
+    if (std::system(nullptr) && std::system(cmd.c_str())) std::fprintf(stderr, "link command failed: %s\n", cmd.c_str());
+  }
   const std::string msg = reprojection_report(cal, results, worldPoints, imagePoints, frame_of_added, residuals_dir);
   std::printf("%s\n", msg.c_str());
   return 0;

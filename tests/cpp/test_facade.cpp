@@ -82,6 +82,22 @@ int main(int argc, char **argv) {
   CHECK(back.size() == 3);
   for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) CHECK(std::fabs(back[1].T_cn_cnm1(i, j) - cams[1].T_cn_cnm1(i, j)) < 1e-11);
 
+  // ---- stereo pair of the same model: rectification entries for cameras 0 and 1 (calibration_nodelet.cpp:428-439);
+  // values are cv2.fisheye.stereoRectify's for the README rig (tests/golden/rectify_golden.json, case 0)
+  {
+    CalibDataVec st(cams.begin(), cams.begin() + 2);
+    st[1].intrinsics.distortion_model = "equidistant";
+    st[1].intrinsics.distortion_coeffs = {-0.0146155, -0.00291494, -0.000681981, 0.000221855};
+    std::stringstream s2;
+    write_calibration(s2, st);
+    const std::string o2 = s2.str();
+    CHECK(o2.find("cam0:\n  rectification_matrix:\n  - [ 0.99999993889,  0.00015082") != std::string::npos);
+    CHECK(o2.find("  projection_matrix:\n  - [439.5640") != std::string::npos);
+    CHECK(o2.find(",  0.00000000000, 712.866") != std::string::npos);
+    CHECK(o2.find("-87.67696") != std::string::npos);
+    CHECK(o2.find("cam1:\n  T_cn_cnm1:\n") != std::string::npos && o2.find("cam1:\n  T_cn_cnm1:\n") < o2.rfind("  rectification_matrix:"));
+  }
+
   // ---- CameraExtrinsics
   CameraExtrinsics P = cams[1].T_cn_cnm1 * cams[2].T_cn_cnm1, Pi = P.inverse(), I = P * Pi;
   for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) CHECK(std::fabs(I(i, j) - (i == j)) < 1e-14);
