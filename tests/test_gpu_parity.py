@@ -330,3 +330,51 @@ def test_full_size_c4_properties(built):
         if k > 0:
             np.testing.assert_allclose(res[k].T_cn_cnm1[:3, 3], c.T_cn_cnm1[:3, 3], atol=2e-4)
     cal.close()
+
+
+@pytest.mark.parametrize("models", [
+    [("equidistant", 2), ("radtan", 5), ("radtan", 8)],     # odd coefficient counts (utils.h:73-78 any number; :115-118 zero-padded to 8)
+    [("radtan", 0), ("equidistant", 0)],                    # no distortion parameters at all
+    [("equidistant", 4), ("equidistant", 8), ("radtan", 2), ("radtan", 8)],   # 25 local columns on the last camera
+])
+def test_distortion_coefficient_counts_and_nonplanar_points(built, models):
+    """every n_dist the reference's templates accept, mixed in one rig, with world points off the z = 0 plane
+    (Point3 has a z; calibrator.cpp:229-249 copies it): blocks and the whole solve against the oracle"""
+    from multicam_calibration_b200 import synth
+    from multicam_calibration_b200.rig import Rig
+    base = synth.make_synthetic_rig(len(models), 14, 17, detect_prob=0.9, mixed_models=False)
+    rng = np.random.default_rng(2)
+    cams = []
+    for (model, nd), c in zip(models, base.cameras):
+        c = c.copy()
+        c.distortion_model = model
+        c.distortion_coeffs = rng.uniform(-2e-3, 2e-3, nd)
+        cams.append(c)
+    world = base.world.copy()
+    world[:, 2] = rng.uniform(-0.01, 0.01, len(world))
+    rig = Rig(cams, base.npts, world, base.image, base.poses)
+    cal, orc = _pair(rig)
+    g, o = cal.normalBlocks(True), orc.normal_blocks(True)
+    for key in ("Hcc", "gc", "Hff", "gf", "Hfc"):
+        assert _rel(g[key], o[key]) <= 1e-10, key
+    _check_solve(cal, orc)
+    cal.close()
+
+
+def test_camera_that_never_saw_the_board(small_rig):
+    """an active camera without a single observation: its blocks stay in the problem with zero columns
+    (Ceres keeps the parameter blocks; Jacobi scale 1, LM diagonal clamped to 1e-6 / radius)"""
+    from multicam_calibration_b200.rig import Rig
+    off = small_rig.frame_offsets()
+    keep = np.ones(small_rig.num_obs, dtype=bool)
+    npts = small_rig.npts.copy()
+    for f in range(small_rig.num_frames):
+        o = off[f] + npts[f, 0]
+        keep[o:o + npts[f, 1]] = False
+    npts[:, 1] = 0
+    rig = Rig(small_rig.cameras, npts, small_rig.world[keep], small_rig.image[keep], small_rig.poses)
+    cal, orc = _pair(rig)
+    sg, so = _check_solve(cal, orc)
+    assert sg.num_reduced_params == so.num_reduced_params
+    p0 = orc.get_params()
+    cal.close()
