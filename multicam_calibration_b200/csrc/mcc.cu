@@ -458,15 +458,18 @@ mcc_status build_structure(mcc_handle* h) {
     CamMeta& m = cm[k];
     std::memset(&m, 0, sizeof(m));
     m.model = c.model; m.nd = c.n_dist; m.intr_off = h->intr_off[k]; m.ext_off = h->ext_off[k];
-    m.ext_col = (k > 0) ? 4 + c.n_dist : -1;
-    m.pose_col = 4 + c.n_dist + (k > 0 ? 6 : 0);
-    m.r_col = m.pose_col + 6;
+    // full local layout [ext 6 (k > 0) | pose 6 | intr n_k | r]: the geometry columns come first so that every
+    // 3-wide block is purely "geometry" or purely "intrinsics / residual" (the expansion epilogue of K1 relies on it)
+    m.ext_col = (k > 0) ? 0 : -1;
+    m.pose_col = (k > 0) ? 6 : 0;
+    m.intr_col = m.pose_col + 6;
+    m.r_col = m.intr_col + 4 + c.n_dist;
     m.ncols = m.r_col + 1;
     m.nb = (m.ncols + 2) / 3;
     m.nblk = m.nb * (m.nb + 1) / 2;
     m.active = c.active;
-    for (int j = 0; j < MAXCAMCOLS; j++) m.red_col[j] = -1;
-    for (int j = 0; j < c.nparam(); j++) m.red_col[j] = h->cam_col[h->intr_off[k] + j];
+    for (int j = 0; j < MAXC; j++) m.red_col[j] = -1;
+    for (int j = 0; j < c.nparam(); j++) m.red_col[m.intr_col + j] = h->cam_col[h->intr_off[k] + j];
     if (k > 0) for (int j = 0; j < 6; j++) m.red_col[m.ext_col + j] = h->cam_col[h->ext_off[k] + j];
     m.lut_off = k * MAXC * MAXC;
     {
@@ -511,14 +514,13 @@ mcc_status build_structure(mcc_handle* h) {
   // reduced column -> (camera, local column)
   std::vector<int2> colmap(std::max(C, 1));
   for (int k = 0; k < ncam; k++) {
-    const int ncc = cm[k].pose_col;   // intrinsic + extrinsic local columns
-    for (int j = 0; j < ncc; j++) if (cm[k].red_col[j] >= 0) colmap[cm[k].red_col[j]] = make_int2(k, j);
+    for (int j = 0; j < cm[k].r_col; j++) if (cm[k].red_col[j] >= 0) colmap[cm[k].red_col[j]] = make_int2(k, j);   // pose columns carry -1
   }
   // camera-camera entries
   std::vector<CcEntry> cc;
   for (int k = 0; k < ncam; k++) {
     if (!h->cams[k].active) continue;
-    const int ncc = cm[k].pose_col;
+    const int ncc = cm[k].r_col;   // every local column but the residual; pose columns carry red_col = -1
     for (int i = 0; i < ncc; i++) {
       if (cm[k].red_col[i] < 0) continue;
       for (int j = i; j < ncc; j++) {
