@@ -394,7 +394,8 @@ mcc_status ensure_device(mcc_handle* h) {
     CU((cudaFuncSetAttribute(k_tile_normal<21, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
     CU((cudaFuncSetAttribute(k_tile_normal<20, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
     CU((cudaFuncSetAttribute(k_tile_normal<28, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
-    CU(cudaFuncSetAttribute(k_schur_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(k_schur_syrk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU(cudaFuncSetAttribute(k_schur_syrk<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(k_solve_cam<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 196 * 1024));
     h->attrs_set = true;
   }
@@ -621,7 +622,7 @@ mcc_status build_structure(mcc_handle* h) {
 
   const int NT = (C + 1 + SY_T - 1) / SY_T;
   h->npairs = NT * (NT + 1) / 2;
-  h->LD = NT * SY_T;
+  h->LD = NT * SY_TS;
   h->sy_gy = (h->npairs + SY_THREADS - 1) / SY_THREADS;
   if (h->sms <= 0) CU(cudaDeviceGetAttribute(&h->sms, cudaDevAttrMultiProcessorCount, h->device));
   const int sms = h->sms;
@@ -867,12 +868,18 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
                                                                     h->d_Lf.p, h->d_Linv.p, h->d_zf.p, h->d_fail.p);
     }
     CU(cudaGetLastError());
-    const size_t smem = ((size_t)SY_FB * 6 * h->LD + SY_FB * 36 + SY_FB * 12) * sizeof(double);
+    const size_t smem0 = ((size_t)SY_FB * 6 * h->LD + 2 * SY_FB * (36 + 18)) * sizeof(double);
+    const size_t smem1 = smem0 + (size_t)SY_FB * 6 * C * sizeof(double);
+    const bool pf = smem1 <= 112 * 1024;   // keep two CTAs per SM; wider systems read Hfc straight from global memory
     dim3 grid(h->sy_gx, h->sy_gy);
     {
       KScope ks(h, KC_SCHUR);
-      k_schur_syrk<<<grid, SY_THREADS, smem, h->stream>>>(h->nslots, C, h->LD, h->npairs, h->d_Hfc2[h->blk].p, h->d_scale_f.p, h->d_scale_c.p, h->d_Lf.p, h->d_Linv.p,
-                                                          h->d_zf.p, h->d_S_part.p);
+      if (pf)
+        k_schur_syrk<true><<<grid, SY_THREADS, smem1, h->stream>>>(h->nslots, C, h->LD, h->npairs, h->d_Hfc2[h->blk].p, h->d_scale_f.p, h->d_scale_c.p, h->d_Lf.p,
+                                                                   h->d_Linv.p, h->d_zf.p, h->d_S_part.p);
+      else
+        k_schur_syrk<false><<<grid, SY_THREADS, smem0, h->stream>>>(h->nslots, C, h->LD, h->npairs, h->d_Hfc2[h->blk].p, h->d_scale_f.p, h->d_scale_c.p, h->d_Lf.p,
+                                                                    h->d_Linv.p, h->d_zf.p, h->d_S_part.p);
     }
     CU(cudaGetLastError());
     const int n = h->npairs * SY_T * SY_T;
