@@ -378,3 +378,15 @@ def test_camera_that_never_saw_the_board(small_rig):
     assert sg.num_reduced_params == so.num_reduced_params
     p0 = orc.get_params()
     cal.close()
+
+
+@pytest.mark.parametrize("ncam", [16, 24])
+def test_wide_rigs_match_oracle(built, ncam):
+    """16 cameras (config c5's rig, 250 camera columns) and 24 cameras (> 256 columns): the reduced system takes the
+    kernel variants that the 8-camera tests never reach (Schur rows read from global memory, Cholesky panels not
+    transposed)."""
+    from multicam_calibration_b200 import synth
+    rig = synth.make_synthetic_rig(ncam, 24, 20260105 + ncam)
+    cal, orc = _pair(rig)
+    _check_solve(cal, orc)
+    cal.close()
