@@ -431,6 +431,83 @@ int tri_index(int bi, int bj, int nb) { return bi * nb - bi * (bi - 1) / 2 + (bj
 
 // Everything that depends on cameras, flags, frame list and masks: reduced column maps
 // (calibrator.cpp:510-521), frames with residual blocks (calibrator.cpp:482-485), tiles.
+// Lane -> (unit, slice) map of the K1 contraction.  A 64-bit shared load is served one half-warp at a time, so the map
+// is searched (backtracking, bounded) for one where the <= 16 lanes of each half-warp hit different 8-byte banks for
+// the unit's own block column and for every partner column; slice q reads rows q, q + ksl, ... and the row stride rs
+// is odd.  Slice counts of the form 2^n or 3 * 2^n only (the reduction handles those).  Falls back to
+// lane = q * nunits + u when no conflict-free map exists (or for the even strides of the MMA path, which ignores it).
+struct LaneSearch {
+  int n;
+  int bank[64][4];
+  int half_of[64];
+  int cnt[2];
+  bool used[2][4][16];
+  long nodes;
+  bool go(int i) {
+    if (++nodes > 200000) return false;
+    if (i == n) return true;
+    for (int hh = 0; hh < 2; hh++) {
+      if (cnt[hh] >= 16) continue;
+      bool ok = true;
+      for (int d = 0; d < 4; d++) if (used[hh][d][bank[i][d]]) ok = false;
+      if (!ok) continue;
+      for (int d = 0; d < 4; d++) used[hh][d][bank[i][d]] = true;
+      cnt[hh]++; half_of[i] = hh;
+      if (go(i + 1)) return true;
+      cnt[hh]--;
+      for (int d = 0; d < 4; d++) used[hh][d][bank[i][d]] = false;
+    }
+    return false;
+  }
+};
+
+static void build_lane_map(CamMeta& m, int rs) {
+  const int nun = m.nunits;
+  static const int cand[] = {8, 6, 4, 3, 2, 1};
+  int lane_of[8][8];
+  bool found = false;
+  int ksl = 1;
+  for (int ci = 0; ci < 6 && !found && (rs & 1); ci++) {
+    ksl = cand[ci];
+    if (nun * ksl > 32) continue;
+    LaneSearch ls;
+    ls.n = nun * ksl; ls.nodes = 0; ls.cnt[0] = ls.cnt[1] = 0;
+    memset(ls.used, 0, sizeof(ls.used));
+    for (int u = 0; u < nun; u++)
+      for (int q = 0; q < ksl; q++)
+        for (int d = 0; d < 4; d++) {
+          int b = u;
+          if (d > 0 && m.unit_o[d - 1][u] >= 0) b = m.unit_o[d - 1][u];
+          ls.bank[u * ksl + q][d] = (rs * q + 3 * b) & 15;
+        }
+    if (ls.go(0)) {
+      found = true;
+      int next[2] = {0, 16};
+      for (int u = 0; u < nun; u++)
+        for (int q = 0; q < ksl; q++) lane_of[u][q] = next[ls.half_of[u * ksl + q]]++;
+    }
+  }
+  if (!found) {
+    ksl = 32 / nun;
+    if (ksl == 5 || ksl == 7) ksl--;
+    for (int u = 0; u < nun; u++) for (int q = 0; q < ksl; q++) lane_of[u][q] = q * nun + u;
+  }
+  m.ksl = ksl;
+  for (int l = 0; l < 32; l++) { m.lane_u[l] = -1; m.lane_q[l] = -1; }
+  for (int u = 0; u < nun; u++) for (int q = 0; q < ksl; q++) { m.lane_u[lane_of[u][q]] = (int8_t)u; m.lane_q[lane_of[u][q]] = (int8_t)q; }
+  int mm = ksl;
+  m.nhalve = 0;
+  for (int r = 0; r < 3; r++) for (int l = 0; l < 32; l++) m.red_src[r][l] = (int8_t)l;
+  for (int r = 0; r < 2; r++) for (int l = 0; l < 32; l++) m.fin_src[r][l] = (int8_t)l;
+  while ((mm & 1) == 0) {
+    mm >>= 1;
+    for (int u = 0; u < nun; u++) for (int q = 0; q < mm; q++) m.red_src[m.nhalve][lane_of[u][q]] = (int8_t)lane_of[u][q + mm];
+    m.nhalve++;
+  }
+  m.mfin = mm;
+  if (mm == 3) for (int u = 0; u < nun; u++) { m.fin_src[0][lane_of[u][0]] = (int8_t)lane_of[u][1]; m.fin_src[1][lane_of[u][0]] = (int8_t)lane_of[u][2]; }
+}
+
 mcc_status build_structure(mcc_handle* h) {
   const int ncam = h->ncam();
   const int F = h->nframes;
@@ -474,24 +551,16 @@ mcc_status build_structure(mcc_handle* h) {
     if (k > 0) for (int j = 0; j < 6; j++) m.red_col[m.ext_col + j] = h->cam_col[h->ext_off[k] + j];
     m.lut_off = k * MAXC * MAXC;
     {
-      // contraction units of the reduced (n_k + 7)-column Gram matrix: walk the block columns, pair up the still
-      // uncovered block pairs that share the column; an odd one out is left to its other column
+      // contraction units of the reduced (n_k + 7)-column Gram matrix: unit u = block column u with itself and with
+      // the block columns at circular distance 1 .. (nb-1)/2; for an even block count the distance nb/2 pairs are
+      // taken by the lower half of the units
       const int rnb = (4 + c.n_dist + 7 + 2) / 3;
-      bool used[9][9];
-      for (int a = 0; a < 9; a++) for (int b = 0; b < 9; b++) used[a][b] = false;
-      m.nunits = 0;
-      for (int sidx = 0; sidx < rnb; sidx++) {
-        std::vector<int> partners;
-        for (int q = 0; q < rnb; q++) if (!used[std::min(sidx, q)][std::max(sidx, q)]) partners.push_back(q);
-        // keep the partner with the highest index for later if the count is odd and that column still has open pairs
-        if (partners.size() % 2 == 1 && partners.back() > sidx) partners.pop_back();
-        for (size_t q = 0; q < partners.size(); q += 2) {
-          const int o1 = partners[q], o2 = q + 1 < partners.size() ? partners[q + 1] : -1;
-          m.unit_s[m.nunits] = (int8_t)sidx; m.unit_o1[m.nunits] = (int8_t)o1; m.unit_o2[m.nunits] = (int8_t)o2;
-          m.nunits++;
-          used[std::min(sidx, o1)][std::max(sidx, o1)] = true;
-          if (o2 >= 0) used[std::min(sidx, o2)][std::max(sidx, o2)] = true;
-        }
+      m.nunits = rnb;
+      for (int d = 0; d < 3; d++) for (int u = 0; u < 8; u++) m.unit_o[d][u] = -1;
+      for (int u = 0; u < rnb; u++) {
+        int nd_ = 0;
+        for (int d = 1; d <= (rnb - 1) / 2; d++) m.unit_o[nd_++][u] = (int8_t)((u + d) % rnb);
+        if (rnb % 2 == 0 && u < rnb / 2) m.unit_o[nd_++][u] = (int8_t)(u + rnb / 2);
       }
     }
     if (c.active) { max_nb = std::max(max_nb, m.nb); max_nblk = std::max(max_nblk, m.nblk); max_red_cols = std::max(max_red_cols, 4 + c.n_dist + 7); }
@@ -511,6 +580,7 @@ mcc_status build_structure(mcc_handle* h) {
   // k_tile_normal<RS, MMA> works on reduced rows of (4 + n_dist) + 7 columns
   if (h->gram_mode == 0) h->rowstride = (max_red_cols + 2) / 3 <= 5 ? 15 : 21;
   else h->rowstride = (max_red_cols + 7) / 8 <= 2 ? 20 : 28;
+  for (int k = 0; k < ncam; k++) build_lane_map(cm[k], h->rowstride);
 
   // reduced column -> (camera, local column)
   std::vector<int2> colmap(std::max(C, 1));
