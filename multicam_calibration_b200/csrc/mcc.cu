@@ -1250,7 +1250,6 @@ mcc_status mcc_add_frames(mcc_handle* h, int nframes, int ncam, const int* npts,
     CU(h->d_aos_i.reserve_keep(2 * (o + n), 2 * o, h->stream));
     CU(cudaMemcpyAsync(h->d_aos_w.p + 3 * o, world_xyz, 3 * n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
     CU(cudaMemcpyAsync(h->d_aos_i.p + 2 * o, image_uv, 2 * n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-    CU(cudaStreamSynchronize(h->stream));
     h->h2d += 5 * n * sizeof(double);
     h->dev_count = o + n;
   } else {
@@ -1274,6 +1273,19 @@ mcc_status mcc_add_frames(mcc_handle* h, int nframes, int ncam, const int* npts,
   h->nframes += nframes;
   h->structure_dirty = h->obs_dirty = h->mask_dirty = true;
   h->params_valid = false;
+  if (direct) {
+    // The copy engine is still busy with the caller's arrays.  For the first bulk load of a data set, use the time:
+    // build the tile structure on the host and queue the AoS -> SoA pass behind the copies, so that the next run
+    // finds both done.  An error here is not this call's to report: the run rebuilds and reports it.
+    if (h->nframes == nframes && nframes >= 64) {
+      if (build_structure(h) == MCC_OK) {
+        if (upload_obs(h) != MCC_OK) h->obs_dirty = h->mask_dirty = true;
+      } else {
+        h->structure_dirty = true;
+      }
+    }
+    CU(cudaStreamSynchronize(h->stream));   // from here on the caller's arrays are no longer referenced
+  }
   return MCC_OK;
 }
 
