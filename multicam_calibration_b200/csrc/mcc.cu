@@ -855,7 +855,7 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo) {
   ST(launch_setup(h, which));
   if (h->ntiles) {
     const size_t smem = (size_t)K1_WARPS * (k1_rows_doubles(h->rowstride) + K1_EXTRA) * sizeof(double);
-    const int grid = (h->ntiles + K1_WARPS - 1) / K1_WARPS;
+    const int grid = (h->ntiles + K1_WARPS * K1_TPW - 1) / (K1_WARPS * K1_TPW);
     KScope ks(h, KC_TILE_NORMAL);
 #define MCC_LAUNCH_TILE_NORMAL(RS, MMA)                                                                                                     \
     k_tile_normal<RS, MMA><<<grid, K1_WARPS * 32, smem, h->stream>>>(h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, \
