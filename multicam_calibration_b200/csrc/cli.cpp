@@ -32,7 +32,10 @@ static void usage() {
   std::fprintf(stderr,
                "usage: mcc_calibrate --calib initial.yaml --corners corners.csv [--init-poses poses.txt] [--output out.yaml]\n"
                "                     [--outlier-pixel-threshold px] [--fix-intrinsics] [--device n] [--residuals-dir dir]\n"
-               "                     [--latest-link name.yaml] [--quiet]\n");
+               "                     [--latest-link name.yaml] [--quiet]\n"
+               "                     [--stage 'cam0:fix_intrinsics=0,fix_extrinsics=1,active=1;cam1:active=0'] ...\n"
+               "  every --stage sets camera flags (the nodelet's set_parameter service) and runs the calibrate() sequence once;\n"
+               "  the result of a stage is the starting point of the next (example_calib_manager.py); no --stage: one run\n");
 }
 
 // calibration_nodelet.cpp:292-345
@@ -79,6 +82,7 @@ static std::string reprojection_report(Calibrator &cal, const CalibDataVec &cali
 
 int main(int argc, char **argv) {
   std::string calib, corners, poses_file, output, residuals_dir, latest_link;
+  std::vector<std::string> stages;
   double outlier = -1.0;
   bool fix_intr = false, quiet = false;
   int device = -1;
@@ -95,6 +99,7 @@ int main(int argc, char **argv) {
     else if (a == "--residuals-dir") residuals_dir = next();
     else if (a == "--latest-link") latest_link = next();
     else if (a == "--quiet") quiet = true;
+    else if (a == "--stage") stages.push_back(next());
     else { usage(); return 2; }
   }
   if (calib.empty() || corners.empty()) { usage(); return 2; }
@@ -153,41 +158,73 @@ int main(int argc, char **argv) {
   }
   std::printf("read %zu frames from %s\n", frame_of_added.size(), corners.c_str());
 
-  // calibrate()  (calibration_nodelet.cpp:196-246)
-  cal.showCameraStatus();
-  cal.runCalibration();
-  if (cal.lastStatus() != MCC_OK) return 1;
-  if (outlier > 0) {
-    cal.removeOutliers(outlier);
-    std::printf("removed outliers, rerunning calibration!\n");
+  if (stages.empty()) stages.push_back("");
+  CalibDataVec results;
+  for (size_t st = 0; st < stages.size(); st++) {
+    // set_parameter service (calibration_nodelet.cpp:257-285): "<camera>:<flag>=<0|1>,...;<camera>:..."
+    if (!stages[st].empty()) {
+      std::stringstream all(stages[st]);
+      std::string one;
+      while (std::getline(all, one, ';')) {
+        const size_t colon = one.find(':');
+        if (colon == std::string::npos) { std::fprintf(stderr, "bad --stage entry: %s\n", one.c_str()); return 2; }
+        const std::string cam = one.substr(0, colon);
+        size_t idx = cameras.size();
+        for (size_t k = 0; k < cameras.size(); k++) if (cameras[k].name == cam) idx = k;
+        if (idx == cameras.size()) { std::fprintf(stderr, "invalid camera name: %s\n", cam.c_str()); return 2; }   // getCameraIndex (:248-255)
+        std::stringstream fl(one.substr(colon + 1));
+        std::string kv;
+        while (std::getline(fl, kv, ',')) {
+          const size_t eq = kv.find('=');
+          if (eq == std::string::npos) { std::fprintf(stderr, "bad --stage flag: %s\n", kv.c_str()); return 2; }
+          const std::string key = kv.substr(0, eq);
+          const bool val = std::atoi(kv.substr(eq + 1).c_str()) != 0;
+          if (key == "fix_intrinsics") cameras[idx].fixIntrinsics = val;
+          else if (key == "fix_extrinsics") cameras[idx].fixExtrinsics = val;
+          else if (key == "active") cameras[idx].active = val;
+          else { std::fprintf(stderr, "invalid parameter: %s\n", key.c_str()); return 2; }
+        }
+      }
+      cal.setCameras(cameras);
+      if (stages.size() > 1) std::printf("--------- calibration stage %zu of %zu ---------\n", st + 1, stages.size());
+    }
+    // calibrate()  (calibration_nodelet.cpp:196-246)
+    cal.showCameraStatus();
     cal.runCalibration();
     if (cal.lastStatus() != MCC_OK) return 1;
-  }
-  CalibDataVec results = cal.getCalibrationResults();
-  if (results.empty()) { std::fprintf(stderr, "empty calibration results, no file written!\n"); return 1; }
-  if (output.empty()) {
-    char buf[64];
-    std::time_t t = std::time(nullptr);
-    std::strftime(buf, sizeof(buf), "%Y-%m-%d-%H-%M-%S", std::localtime(&t));   // make_filename (:19-26)
-    output = std::string("calibration_output-") + buf + ".yaml";
-  }
-  std::printf("writing calibration to %s\n", output.c_str());
-  {
-    std::ofstream of(output);
-    write_calibration(of, results, T_imu_body);
-  }
-  // updateCameras (:455-469): results become the next run's initial values; flags are kept
-  for (size_t k = 0; k < cameras.size(); k++) {
-    cameras[k].intrinsics = results[k].intrinsics;
-    cameras[k].T_cn_cnm1 = results[k].T_cn_cnm1;
-    cameras[k].T_cam_imu = results[k].T_cam_imu;
-  }
-  cal.setCameras(cameras);   // (:227) params_ of the finished run stay in place for the test below
-  write_calibration(std::cout, results, T_imu_body);
-  if (!latest_link.empty()) {
-    // "ln -sf <file> <calib_dir>/<latest_link_name>" (calibration_nodelet.cpp:232-235)
-    const std::string cmd = "ln -sf " + output + " " + latest_link;
-    if (std::system(nullptr) && std::system(cmd.c_str())) std::fprintf(stderr, "link command failed: %s\n", cmd.c_str());
+    if (outlier > 0) {
+      cal.removeOutliers(outlier);
+      std::printf("removed outliers, rerunning calibration!\n");
+      cal.runCalibration();
+      if (cal.lastStatus() != MCC_OK) return 1;
+    }
+    results = cal.getCalibrationResults();
+    if (results.empty()) { std::fprintf(stderr, "empty calibration results, no file written!\n"); return 1; }
+    std::string out_name = output;
+    if (out_name.empty()) {
+      char buf[64];
+      std::time_t t = std::time(nullptr);
+      std::strftime(buf, sizeof(buf), "%Y-%m-%d-%H-%M-%S", std::localtime(&t));   // make_filename (:19-26)
+      out_name = std::string("calibration_output-") + buf + ".yaml";
+    }
+    std::printf("writing calibration to %s\n", out_name.c_str());
+    {
+      std::ofstream of(out_name);
+      write_calibration(of, results, T_imu_body);
+    }
+    // updateCameras (:455-469): results become the next run's initial values; flags are kept
+    for (size_t k = 0; k < cameras.size(); k++) {
+      cameras[k].intrinsics = results[k].intrinsics;
+      cameras[k].T_cn_cnm1 = results[k].T_cn_cnm1;
+      cameras[k].T_cam_imu = results[k].T_cam_imu;
+    }
+    cal.setCameras(cameras);   // (:227) params_ of the finished run stay in place for the test below
+    write_calibration(std::cout, results, T_imu_body);
+    if (!latest_link.empty()) {
+      // "ln -sf <file> <calib_dir>/<latest_link_name>" (calibration_nodelet.cpp:232-235)
+      const std::string cmd = "ln -sf " + out_name + " " + latest_link;
+      if (std::system(nullptr) && std::system(cmd.c_str())) std::fprintf(stderr, "link command failed: %s\n", cmd.c_str());
+    }
   }
   const std::string msg = reprojection_report(cal, results, worldPoints, imagePoints, frame_of_added, residuals_dir);
   std::printf("%s\n", msg.c_str());

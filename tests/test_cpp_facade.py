@@ -82,3 +82,69 @@ def test_cli_radtan_fixture_matches_reference_log(built, tmp_path):
     assert "max error: 2.37361e-05 px at frame: 84 for cam: 0" in so
     res = np.loadtxt(tmp_path / "residuals_cam0.txt")
     assert res.shape == (ref["num_residuals"] // 2, 10)
+
+
+@pytest.mark.gpu
+def test_cli_staged_workflow_matches_api(built, tmp_path):
+    """the staged calibration of example_calib_manager.py:22-52 (cam0 intrinsics, then cam1 intrinsics, then the
+    extrinsics between them; every stage = set_parameter calls + one calibrate(), calibration_nodelet.cpp:196-285)
+    through `mcc_calibrate --stage ...`, against the same sequence driven through the C ABI from Python"""
+    from multicam_calibration_b200 import capi, synth
+    from multicam_calibration_b200.rig import Rig
+    rig = synth.make_synthetic_rig(2, 40, 20260107, readme_stereo=True)
+    for k, c in enumerate(rig.cameras):
+        c.name, c.rostopic, c.resolution = "cam%d" % k, "/cam%d/image_raw" % k, (1280, 1024)
+    # the csv carries %f text parsed as float (calibration_nodelet.cpp:566): narrow the rig the same way
+    nar = lambda a: np.array([float(np.float32(float("%f" % x))) for x in a.ravel()]).reshape(a.shape)
+    world = np.concatenate([nar(rig.world[:, :2]), np.zeros((rig.num_obs, 1))], axis=1)
+    image = nar(rig.image)
+    rig = Rig(rig.cameras, rig.npts, world, image, rig.poses)
+    with open(tmp_path / "corners.csv", "w") as f:
+        o = 0
+        for fr in range(rig.num_frames):
+            for k in range(2):
+                for i in range(rig.npts[fr, k]):
+                    f.write("%d, intrinsics, %d, %f, %f, %f, %f\n" % (fr, k, world[o, 0], world[o, 1], image[o, 0], image[o, 1]))
+                    o += 1
+    with open(tmp_path / "initial.yaml", "w") as f:
+        for k, c in enumerate(rig.cameras):
+            f.write("cam%d:\n  camera_model: pinhole\n  intrinsics: [%s]\n  distortion_model: %s\n  distortion_coeffs: [%s]\n"
+                    % (k, ", ".join(repr(float(x)) for x in c.intrinsics), c.distortion_model, ", ".join(repr(float(x)) for x in c.distortion_coeffs)))
+            if k > 0:
+                f.write("  T_cn_cnm1:\n" + "".join("  - [%s]\n" % ", ".join(repr(float(x)) for x in row) for row in c.T_cn_cnm1))
+            f.write("  resolution: [1280, 1024]\n  rostopic: %s\n" % c.rostopic)
+    np.savetxt(tmp_path / "poses.txt", rig.poses.reshape(rig.num_frames, 16), fmt="%.17g")
+    stages = [((False, True, True), (True, True, False)), ((True, True, False), (False, True, True)), ((True, True, True), (True, False, True))]
+    args = []
+    for st in stages:
+        args += ["--stage", ";".join("cam%d:fix_intrinsics=%d,fix_extrinsics=%d,active=%d" % ((k,) + tuple(int(b) for b in fl)) for k, fl in enumerate(st))]
+    out_yaml = tmp_path / "staged.yaml"
+    r = subprocess.run([os.path.join(PKG, "mcc_calibrate"), "--calib", str(tmp_path / "initial.yaml"), "--corners", str(tmp_path / "corners.csv"),
+                        "--init-poses", str(tmp_path / "poses.txt"), "--output", str(out_yaml), "--quiet"] + args, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("writing calibration to") == 3
+    # the same three stages through the ABI
+    cal = capi.calibrator_from_rig(rig, device=0)
+    cams = [c.copy() for c in rig.cameras]
+    for st in stages:
+        for k, fl in enumerate(st):
+            cams[k].fix_intrinsics, cams[k].fix_extrinsics, cams[k].active = fl
+        cal.setCameras(cams)
+        cal.runCalibration()
+        for k, res in enumerate(cal.getCalibrationResults()):
+            cams[k].intrinsics, cams[k].distortion_coeffs, cams[k].T_cn_cnm1 = res.intrinsics, res.distortion_coeffs, res.T_cn_cnm1
+    cal.close()
+    y = open(out_yaml).read()
+    import re
+    got = [np.array([float(x) for x in m.split(",")]) for m in re.findall(r"  intrinsics: \[(.*)\]", y)]
+    gotd = [np.array([float(x) for x in m.split(",")]) for m in re.findall(r"  distortion_coeffs: \[(.*)\]", y)]
+    tail = y[y.index("T_cn_cnm1:"):]
+    rows = [np.array([float(x) for x in m.split(",")]) for m in re.findall(r"  - \[(.*)\]", tail)]
+    assert len(got) == 2 and len(rows) >= 4
+    for k in range(2):
+        np.testing.assert_allclose(got[k], cams[k].intrinsics, rtol=2e-5)            # the YAML prints 6 significant digits
+        np.testing.assert_allclose(gotd[k], cams[k].distortion_coeffs, rtol=2e-5, atol=1e-9)
+    np.testing.assert_allclose(np.array(rows[:4]), cams[1].T_cn_cnm1, rtol=2e-5, atol=1e-9)
+    # and the stages did something: the generating cameras are recovered from the perturbed start
+    for k, c in enumerate(rig_truth := synth.make_synthetic_rig(2, 40, 20260107, readme_stereo=True).truth["cameras"]):
+        np.testing.assert_allclose(cams[k].intrinsics, c.intrinsics, rtol=5e-3)
