@@ -729,7 +729,7 @@ mcc_status build_structure(mcc_handle* h) {
   CU(h->d_Lf.reserve(ns * 36));
   CU(h->d_cost_f.reserve(ns)); CU(h->d_gmax_f.reserve(ns)); CU(h->d_xn2_f.reserve(ns)); CU(h->d_newcost_f.reserve(ns));
   CU(h->d_mcc_f.reserve(ns)); CU(h->d_dx2_f.reserve(ns)); CU(h->d_xn2c_f.reserve(ns));
-  CU(h->d_cc_part.reserve((size_t)std::max(h->ncc_chunks, 1) * h->cc_maxne)); CU(h->d_cc_sum.reserve(std::max(h->E, 1)));
+  CU(h->d_cc_part.reserve((size_t)std::max(h->ncc_chunks, 1) * h->cc_maxne)); CU(h->d_cc_sum.reserve((size_t)h->E + COMM_SCAL + 2 * 64));
   for (int b = 0; b < 2; b++) { CU(h->d_Hcc2[b].reserve((size_t)std::max(C, 1) * std::max(C, 1))); CU(h->d_gc2[b].reserve(std::max(C, 1))); }
   CU(h->d_scale_c.reserve(std::max(C, 1))); CU(h->d_scale_f.reserve(ns * 6));
   CU(h->d_S_part.reserve((size_t)h->sy_gx * h->npairs * SY_T * SY_T)); CU(h->d_S_sum.reserve((size_t)h->npairs * SY_T * SY_T));
@@ -851,7 +851,13 @@ mcc_status allreduce(mcc_handle* h, double* p, size_t n, int op) {
 
 // K1 at the current parameters: blocks, cost, gradient norm, |x|^2 -> d_scal[0..2], [8..9]
 // blocks of parameter set `which` into block set `bo`
-mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo) {
+// Several ranks: the camera-camera entries and every scalar of the iteration travel in ONE all-reduce (sum) over
+// d_cc_sum = [entries E | 6 scalars | gradient max per rank | failure flag per rank]; k_scatter_cc unpacks it.
+// step_scalars: launch_step has already put its three sums and the failure flag into the tail (and cleared the buffer).
+mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, bool step_scalars = false) {
+  const bool multi = h->nranks > 1;
+  double* tail = h->d_cc_sum.p + h->E;
+  if (!step_scalars) CU(cudaMemsetAsync(h->d_cc_sum.p, 0, ((size_t)h->E + COMM_SCAL + 2 * 64) * sizeof(double), h->stream));
   ST(launch_setup(h, which));
   if (h->ntiles) {
     const size_t smem = (size_t)K1_WARPS * (k1_rows_doubles(h->rowstride) + K1_EXTRA) * sizeof(double);
@@ -883,7 +889,6 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo) {
     CU(cudaGetLastError());
     {
       KScope ks(h, KC_REDUCE);
-      CU(cudaMemsetAsync(h->d_cc_sum.p, 0, (size_t)h->E * sizeof(double), h->stream));
       k_cc_reduce<<<h->ncam(), 1024, (size_t)CCR_S * h->cc_maxne * sizeof(double), h->stream>>>(h->ncam(), h->d_cam_chunk0.p, h->d_cc_chunks.p, h->cc_maxne,
                                                                                                h->d_cc_part.p, h->d_cc_sum.p);
     }
@@ -891,24 +896,19 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo) {
   }
   ReduceJobs jobs;
   std::memset(&jobs, 0, sizeof(jobs));
-  jobs.j[0] = ReduceJob{h->d_cost_f.p, 0};
-  jobs.j[1] = ReduceJob{h->d_xn2_f.p, 0};
-  jobs.j[2] = ReduceJob{h->d_gmax_f.p, 1};
+  jobs.j[0] = ReduceJob{h->d_cost_f.p, 0, multi ? tail + 0 : nullptr};
+  jobs.j[1] = ReduceJob{h->d_xn2_f.p, 0, multi ? tail + 1 : nullptr};
+  jobs.j[2] = ReduceJob{h->d_gmax_f.p, 1, multi ? tail + COMM_SCAL + h->rank : nullptr};
   {
     KScope ks(h, KC_REDUCE);
     k_reduce_arrays<<<3, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p);
   }
   CU(cudaGetLastError());
-  if (h->nranks > 1) {
-    NC(nccl().GroupStart());
-    ST(allreduce(h, h->d_cc_sum.p, h->E, ncclSum_));
-    ST(allreduce(h, h->d_scal.p, 2, ncclSum_));
-    ST(allreduce(h, h->d_scal.p + 2, 1, ncclMax_));
-    NC(nccl().GroupEnd());
-  }
+  if (multi) ST(allreduce(h, h->d_cc_sum.p, (size_t)h->E + COMM_SCAL + 2 * h->nranks, ncclSum_));
   {
     KScope ks(h, KC_REDUCE);
-    k_scatter_cc<<<1, 1024, 0, h->stream>>>(h->C, h->E, h->d_cc.p, h->d_cc_sum.p, h->d_col_param.p, h->d_camp[which].p, h->d_Hcc2[bo].p, h->d_gc2[bo].p, h->d_scal.p + 8);
+    k_scatter_cc<<<1, 1024, 0, h->stream>>>(h->C, h->E, h->d_cc.p, h->d_cc_sum.p, h->d_col_param.p, h->d_camp[which].p, h->d_Hcc2[bo].p, h->d_gc2[bo].p, h->d_scal.p + 8,
+                                             h->nranks, h->d_scal.p, h->d_fail.p);
   }
   CU(cudaGetLastError());
   return MCC_OK;
@@ -984,14 +984,31 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     }
     CU(cudaGetLastError());
   }
-  if (speculate) ST(launch_jacobian(h, o.use_loss, cand, 1 - h->blk));   // cost, |x|^2, gradient norm -> d_scal[0..2], [8..9]
-  else ST(launch_cost(h, cand, o.use_loss, h->d_newcost_f.p, nullptr));
   ReduceJobs jobs;
   std::memset(&jobs, 0, sizeof(jobs));
-  jobs.j[0] = ReduceJob{speculate ? h->d_cost_f.p : h->d_newcost_f.p, 0};
-  jobs.j[1] = ReduceJob{h->d_mcc_f.p, 0};
-  jobs.j[2] = ReduceJob{h->d_dx2_f.p, 0};
-  jobs.j[3] = ReduceJob{h->d_xn2c_f.p, 0};
+  if (speculate) {
+    // the step's scalars are reduced first; with several ranks they (and the failure flag) go into the tail of the
+    // buffer that the Jacobian pass all-reduces, so the whole iteration has two collectives: this one and K2's
+    const bool multi = h->nranks > 1;
+    double* tail = h->d_cc_sum.p + h->E;
+    if (multi) CU(cudaMemsetAsync(h->d_cc_sum.p, 0, ((size_t)h->E + COMM_SCAL + 2 * 64) * sizeof(double), h->stream));
+    jobs.j[0] = ReduceJob{h->d_mcc_f.p, 0, multi ? tail + 3 : h->d_scal.p + 4};
+    jobs.j[1] = ReduceJob{h->d_dx2_f.p, 0, multi ? tail + 4 : h->d_scal.p + 5};
+    jobs.j[2] = ReduceJob{h->d_xn2c_f.p, 0, multi ? tail + 5 : h->d_scal.p + 6};
+    jobs.j[3] = ReduceJob{reinterpret_cast<const double*>(h->d_fail.p), 2, tail + COMM_SCAL + h->nranks + h->rank};
+    {
+      KScope ks(h, KC_REDUCE);
+      k_reduce_arrays<<<multi ? 4 : 3, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p);
+    }
+    CU(cudaGetLastError());
+    ST(launch_jacobian(h, o.use_loss, cand, 1 - h->blk, multi));   // cost, |x|^2, gradient norm -> d_scal[0..2], [8..9]
+    return MCC_OK;
+  }
+  ST(launch_cost(h, cand, o.use_loss, h->d_newcost_f.p, nullptr));
+  jobs.j[0] = ReduceJob{h->d_newcost_f.p, 0, nullptr};
+  jobs.j[1] = ReduceJob{h->d_mcc_f.p, 0, nullptr};
+  jobs.j[2] = ReduceJob{h->d_dx2_f.p, 0, nullptr};
+  jobs.j[3] = ReduceJob{h->d_xn2c_f.p, 0, nullptr};
   {
     KScope ks(h, KC_REDUCE);
     k_reduce_arrays<<<4, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p + 3);
@@ -1553,6 +1570,7 @@ mcc_status mcc_comm_unique_id(unsigned char id[MCC_UNIQUE_ID_BYTES]) {
 mcc_status mcc_comm_init(mcc_handle* h, int nranks, int rank, const unsigned char id[MCC_UNIQUE_ID_BYTES]) {
   if (!h || !id || nranks < 1 || rank < 0 || rank >= nranks) return fail(h, MCC_ERR_BAD_ARG, "bad communicator arguments");
   if (nranks == 1) { h->nranks = 1; h->rank = 0; return MCC_OK; }
+  if (nranks > 64) return fail(h, MCC_ERR_BAD_ARG, "at most 64 ranks (per-rank slots of the merged all-reduce)");
   if (!nccl().ok()) return fail(h, MCC_ERR_NCCL, "libnccl.so.2 not found");
   ST(ensure_device(h));
   ncclUniqueId u;
