@@ -50,6 +50,12 @@ struct NcclApi {
   int (*GroupStart)() = nullptr;
   int (*GroupEnd)() = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
+  // symmetric-memory windows (NCCL >= 2.27), optional
+  int (*MemAlloc)(void**, size_t) = nullptr;
+  int (*MemFree)(void*) = nullptr;
+  int (*CommWindowRegister)(ncclComm_t, void*, size_t, void**, int) = nullptr;
+  int (*CommWindowDeregister)(ncclComm_t, void*) = nullptr;
+  bool has_windows() const { return MemAlloc && MemFree && CommWindowRegister && CommWindowDeregister; }
   bool ok() const { return lib && GetUniqueId && CommInitRank && AllReduce && GroupStart && GroupEnd; }
 };
 NcclApi& nccl() {
@@ -70,6 +76,10 @@ NcclApi& nccl() {
       api.GroupStart = (int (*)())dlsym(api.lib, "ncclGroupStart");
       api.GroupEnd = (int (*)())dlsym(api.lib, "ncclGroupEnd");
       api.GetErrorString = (const char* (*)(int))dlsym(api.lib, "ncclGetErrorString");
+      api.MemAlloc = (int (*)(void**, size_t))dlsym(api.lib, "ncclMemAlloc");
+      api.MemFree = (int (*)(void*))dlsym(api.lib, "ncclMemFree");
+      api.CommWindowRegister = (int (*)(ncclComm_t, void*, size_t, void**, int))dlsym(api.lib, "ncclCommWindowRegister");
+      api.CommWindowDeregister = (int (*)(ncclComm_t, void*))dlsym(api.lib, "ncclCommWindowDeregister");
     }
   }
   return api;
@@ -292,6 +302,16 @@ struct mcc_handle {
   int blk = 0;
   DBuf<double> d_setup, d_G, d_tile_s, d_Lf, d_cost_f, d_gmax_f, d_xn2_f, d_newcost_f, d_mcc_f, d_dx2_f, d_xn2c_f;
   DBuf<double> d_cc_part, d_cc_sum, d_scale_c, d_scale_f, d_S_part, d_S_sum, d_M, d_yc, d_ysc, d_scal;
+  // several ranks: the two all-reduced buffers live in NCCL symmetric-memory windows when the library has them
+  double* win_S = nullptr; double* win_cc = nullptr;
+  void* wh_S = nullptr; void* wh_cc = nullptr;
+  size_t win_S_n = 0, win_cc_n = 0;
+  // ... or, on one node with peer access, in a CUDA IPC window that every rank maps (k_peer_allreduce)
+  PeerWin pw{};
+  uint4* peer_own = nullptr;            // this rank's window (cudaMalloc)
+  size_t peer_nS = 0, peer_nC = 0;      // slot sizes the window was laid out for
+  unsigned long long peer_seq[2] = {0, 0};
+  bool peer_on = false, peer_failed = false;
   double* h_scal = nullptr;            // pinned mirror of d_scal
   int* h_fail = nullptr;
   int asm_grid = 0, sy_gx = 0, sy_gy = 0;
@@ -798,6 +818,9 @@ mcc_status download_params(mcc_handle* h) {
   return MCC_OK;
 }
 
+mcc_status ensure_comm_windows(mcc_handle* h);
+mcc_status ensure_peer_window(mcc_handle* h);
+
 mcc_status prepare(mcc_handle* h) {
   if (h->cams.empty() || h->nframes == 0) return fail(h, MCC_ERR_NO_DATA, "no data to run on!");
   ST(ensure_device(h));
@@ -805,6 +828,8 @@ mcc_status prepare(mcc_handle* h) {
     if (c.active && c.model != MCC_MODEL_EQUIDISTANT && c.model != MCC_MODEL_RADTAN) return fail(h, MCC_ERR_BAD_MODEL, "unknown distortion model: %d", c.model);
   if (!h->params_valid || (long long)h->params.size() != mcc_num_params(h)) init_params(h);
   if (h->structure_dirty) ST(build_structure(h));
+  ST(ensure_peer_window(h));
+  if (!h->peer_on) ST(ensure_comm_windows(h));
   ST(upload_obs(h));
   ST(upload_params(h));
   return MCC_OK;
@@ -843,6 +868,145 @@ mcc_status launch_cost(mcc_handle* h, int which, int use_loss, double* cost_f_ou
   return MCC_OK;
 }
 
+inline double* S_sum_buf(mcc_handle* h) { return h->win_S ? h->win_S : h->d_S_sum.p; }
+inline double* cc_sum_buf(mcc_handle* h) { return h->win_cc ? h->win_cc : h->d_cc_sum.p; }
+
+void free_comm_windows(mcc_handle* h) {
+  if (h->wh_S) nccl().CommWindowDeregister(h->comm, h->wh_S);
+  if (h->wh_cc) nccl().CommWindowDeregister(h->comm, h->wh_cc);
+  if (h->win_S) nccl().MemFree(h->win_S);
+  if (h->win_cc) nccl().MemFree(h->win_cc);
+  h->wh_S = h->wh_cc = nullptr; h->win_S = h->win_cc = nullptr; h->win_S_n = h->win_cc_n = 0;
+}
+
+// Collective over the ranks (every rank prepares the same structure): the Schur tile pairs and the merged
+// camera-camera / scalar buffer move into ncclMemAlloc'ed memory registered as symmetric windows, which lets NCCL
+// pick its low-latency NVLink kernels for these ~50 KB all-reduces.  Only with MCC_NCCL_SYMMETRIC=1.
+mcc_status ensure_comm_windows(mcc_handle* h) {
+  if (h->nranks <= 1 || !nccl().has_windows()) return MCC_OK;
+  const char* env = std::getenv("MCC_NCCL_SYMMETRIC");
+  if (!env || env[0] != '1') return MCC_OK;   // opt-in: measured no gain at 2 and 8 GPUs
+  const size_t nS = (size_t)h->npairs * SY_T * SY_T, nC = (size_t)h->E + COMM_SCAL + 2 * 64;
+  if (h->win_S && h->win_S_n == nS && h->win_cc_n == nC) return MCC_OK;
+  CU(cudaStreamSynchronize(h->stream));
+  free_comm_windows(h);
+  auto round_up = [](size_t b) { return (b + 4095) / 4096 * 4096; };
+  void *pS = nullptr, *pC = nullptr;
+  if (nccl().MemAlloc(&pS, round_up(nS * sizeof(double))) != 0 || nccl().MemAlloc(&pC, round_up(nC * sizeof(double))) != 0) {
+    if (pS) nccl().MemFree(pS);
+    return MCC_OK;   // plain buffers
+  }
+  h->win_S = (double*)pS; h->win_cc = (double*)pC; h->win_S_n = nS; h->win_cc_n = nC;
+  const int rS = nccl().CommWindowRegister(h->comm, pS, round_up(nS * sizeof(double)), &h->wh_S, 1 /* NCCL_WIN_COLL_SYMMETRIC */);
+  const int rC = nccl().CommWindowRegister(h->comm, pC, round_up(nC * sizeof(double)), &h->wh_cc, 1);
+  if (rS != 0) h->wh_S = nullptr;    // the memory is still usable as an ordinary buffer
+  if (rC != 0) h->wh_cc = nullptr;
+  if (std::getenv("MCC_COMM_DEBUG"))
+    std::fprintf(stderr, "[mcc rank %d] symmetric windows: S %zu B -> %s, cc %zu B -> %s\n", h->rank, round_up(nS * sizeof(double)), rS == 0 ? "registered" : "plain",
+                 round_up(nC * sizeof(double)), rC == 0 ? "registered" : "plain");
+  CU(cudaMemsetAsync(pS, 0, round_up(nS * sizeof(double)), h->stream));
+  CU(cudaMemsetAsync(pC, 0, round_up(nC * sizeof(double)), h->stream));
+  return MCC_OK;
+}
+
+void free_peer_window(mcc_handle* h) {
+  if (!h->peer_own) return;
+  cudaStreamSynchronize(h->stream);
+  if (h->comm) {   // nobody may still be storing into a window that is about to go away
+    nccl().AllReduce(h->d_fail.p, h->d_fail.p, 1, ncclInt32_, ncclMax_, h->comm, h->stream);
+    cudaStreamSynchronize(h->stream);
+  }
+  for (int r = 0; r < h->pw.nranks; r++)
+    if (r != h->pw.rank && h->pw.base[r]) cudaIpcCloseMemHandle(h->pw.base[r]);
+  cudaFree(h->peer_own);
+  h->peer_own = nullptr; h->peer_on = false; h->peer_nS = h->peer_nC = 0;
+  h->pw = PeerWin{};
+}
+
+// Collective over the ranks: (re)creates the peer windows for the current sizes of the two exchanges.  Any failure
+// (more than PEER_MAX ranks, ranks on different nodes, no peer access, CUDA IPC not permitted) leaves the NCCL path
+// in place -- on ALL ranks, the outcome is agreed upon by an all-reduce.  MCC_P2P=0 disables the attempt.
+mcc_status ensure_peer_window(mcc_handle* h) {
+  if (h->nranks <= 1) return MCC_OK;
+  const char* env = std::getenv("MCC_P2P");
+  if ((env && env[0] == '0') || h->nranks > PEER_MAX) return MCC_OK;
+  const size_t nS = (size_t)h->npairs * SY_T * SY_T, nC = (size_t)h->E + COMM_SCAL + 2 * 64;
+  if ((h->peer_own || h->peer_failed) && h->peer_nS == nS && h->peer_nC == nC) return MCC_OK;
+  free_peer_window(h);
+  h->peer_failed = false;
+  const int R = h->nranks;
+  const size_t cells = 2 * (size_t)R * (nS + nC);   // 2 parities x R slots per exchange, 16 bytes per value
+  int bad = 0;
+  if (cudaMalloc((void**)&h->peer_own, cells * sizeof(uint4)) != cudaSuccess) { h->peer_own = nullptr; bad = 1; }
+  cudaIpcMemHandle_t mine;
+  std::memset(&mine, 0, sizeof(mine));
+  if (!bad) {
+    CU(cudaMemsetAsync(h->peer_own, 0, cells * sizeof(uint4), h->stream));
+    if (cudaIpcGetMemHandle(&mine, h->peer_own) != cudaSuccess) bad = 1;
+  }
+  cudaGetLastError();
+  // gather the handles: every rank fills its own 64 bytes of a zeroed table, the int32 sum is the concatenation
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  const size_t tab_ints = (size_t)R * 16 + 1;   // + the failure count
+  std::vector<int> tab(tab_ints, 0);
+  std::memcpy(&tab[(size_t)h->rank * 16], &mine, 64);
+  tab[(size_t)R * 16] = bad;
+  int* d_tab = nullptr;
+  CU(cudaMalloc((void**)&d_tab, tab_ints * sizeof(int)));
+  CU(cudaMemcpyAsync(d_tab, tab.data(), tab_ints * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+  NC(nccl().AllReduce(d_tab, d_tab, tab_ints, ncclInt32_, ncclSum_, h->comm, h->stream));
+  CU(cudaMemcpyAsync(tab.data(), d_tab, tab_ints * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  bad = tab[(size_t)R * 16];
+  PeerWin pw{};
+  pw.nranks = R; pw.rank = h->rank;
+  if (!bad) {
+    for (int r = 0; r < R; r++) {
+      if (r == h->rank) { pw.base[r] = h->peer_own; continue; }
+      cudaIpcMemHandle_t hd;
+      std::memcpy(&hd, &tab[(size_t)r * 16], 64);
+      void* p = nullptr;
+      if (cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { bad = 1; cudaGetLastError(); break; }
+      pw.base[r] = (uint4*)p;
+    }
+  }
+  // second agreement: did everybody manage to map everybody?
+  int one = bad;
+  CU(cudaMemcpyAsync(d_tab, &one, sizeof(int), cudaMemcpyHostToDevice, h->stream));
+  NC(nccl().AllReduce(d_tab, d_tab, 1, ncclInt32_, ncclSum_, h->comm, h->stream));
+  CU(cudaMemcpyAsync(&one, d_tab, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  cudaFree(d_tab);
+  h->pw = pw;
+  if (std::getenv("MCC_COMM_DEBUG")) std::fprintf(stderr, "[mcc rank %d] peer window %zu B: %s\n", h->rank, cells * sizeof(uint4), one == 0 ? "mapped on all ranks" : "not available, NCCL");
+  if (one != 0) {
+    for (int r = 0; r < R; r++)
+      if (r != h->rank && pw.base[r]) cudaIpcCloseMemHandle(pw.base[r]);
+    if (h->peer_own) cudaFree(h->peer_own);
+    h->peer_own = nullptr; h->pw = PeerWin{}; h->peer_on = false;
+    // remember the sizes so that the attempt is not repeated on every run
+    h->peer_nS = nS; h->peer_nC = nC; h->peer_failed = true;
+    return MCC_OK;
+  }
+  h->peer_nS = nS; h->peer_nC = nC; h->peer_seq[0] = h->peer_seq[1] = 0; h->peer_on = true;
+  return MCC_OK;
+}
+
+// exchange 0: Schur tile pairs (n = peer_nS), exchange 1: camera-camera entries + scalars (n <= peer_nC)
+mcc_status peer_allreduce(mcc_handle* h, int ex, double* p, size_t n) {
+  const int R = h->nranks;
+  const unsigned long long seq = ++h->peer_seq[ex];
+  const size_t slot_n = ex == 0 ? h->peer_nS : h->peer_nC;
+  if (n > slot_n) return fail(h, MCC_ERR_NCCL, "peer window laid out for another size");
+  const size_t base = ex == 0 ? 0 : 2 * (size_t)R * h->peer_nS;
+  const size_t off = base + (seq & 1) * (size_t)R * slot_n;
+  // the sequence number in the cells is 32 bits and never 0 (0 = a fresh window)
+  const unsigned int seq32 = (unsigned int)(seq % 0xffffffffull) + 1u;
+  k_peer_allreduce<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->pw, p, (int)n, off, seq32, h->d_fail.p);
+  CU(cudaGetLastError());
+  return MCC_OK;
+}
+
 mcc_status allreduce(mcc_handle* h, double* p, size_t n, int op) {
   if (h->nranks <= 1 || n == 0) return MCC_OK;
   NC(nccl().AllReduce(p, p, n, ncclFloat64_, op, h->comm, h->stream));
@@ -856,8 +1020,8 @@ mcc_status allreduce(mcc_handle* h, double* p, size_t n, int op) {
 // step_scalars: launch_step has already put its three sums and the failure flag into the tail (and cleared the buffer).
 mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, bool step_scalars = false) {
   const bool multi = h->nranks > 1;
-  double* tail = h->d_cc_sum.p + h->E;
-  if (!step_scalars) CU(cudaMemsetAsync(h->d_cc_sum.p, 0, ((size_t)h->E + COMM_SCAL + 2 * 64) * sizeof(double), h->stream));
+  double* tail = cc_sum_buf(h) + h->E;
+  if (!step_scalars) CU(cudaMemsetAsync(cc_sum_buf(h), 0, ((size_t)h->E + COMM_SCAL + 2 * 64) * sizeof(double), h->stream));
   ST(launch_setup(h, which));
   if (h->ntiles) {
     const size_t smem = (size_t)K1_WARPS * (k1_rows_doubles(h->rowstride) + K1_EXTRA) * sizeof(double);
@@ -890,7 +1054,7 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, bool 
     {
       KScope ks(h, KC_REDUCE);
       k_cc_reduce<<<h->ncam(), 1024, (size_t)CCR_S * h->cc_maxne * sizeof(double), h->stream>>>(h->ncam(), h->d_cam_chunk0.p, h->d_cc_chunks.p, h->cc_maxne,
-                                                                                               h->d_cc_part.p, h->d_cc_sum.p);
+                                                                                               h->d_cc_part.p, cc_sum_buf(h));
     }
     CU(cudaGetLastError());
   }
@@ -904,10 +1068,14 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, bool 
     k_reduce_arrays<<<3, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p);
   }
   CU(cudaGetLastError());
-  if (multi) ST(allreduce(h, h->d_cc_sum.p, (size_t)h->E + COMM_SCAL + 2 * h->nranks, ncclSum_));
+  if (multi) {
+    const size_t n = (size_t)h->E + COMM_SCAL + 2 * h->nranks;
+    if (h->peer_on) ST(peer_allreduce(h, 1, cc_sum_buf(h), n));
+    else ST(allreduce(h, cc_sum_buf(h), n, ncclSum_));
+  }
   {
     KScope ks(h, KC_REDUCE);
-    k_scatter_cc<<<1, 1024, 0, h->stream>>>(h->C, h->E, h->d_cc.p, h->d_cc_sum.p, h->d_col_param.p, h->d_camp[which].p, h->d_Hcc2[bo].p, h->d_gc2[bo].p, h->d_scal.p + 8,
+    k_scatter_cc<<<1, 1024, 0, h->stream>>>(h->C, h->E, h->d_cc.p, cc_sum_buf(h), h->d_col_param.p, h->d_camp[which].p, h->d_Hcc2[bo].p, h->d_gc2[bo].p, h->d_scal.p + 8,
                                              h->nranks, h->d_scal.p, h->d_fail.p);
   }
   CU(cudaGetLastError());
@@ -955,10 +1123,11 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     const int n = h->npairs * SY_T * SY_T;
     {
       KScope ks(h, KC_REDUCE);
-      k_reduce_rows<<<(n + RR_E - 1) / RR_E, RR_E * RR_S, 0, h->stream>>>(h->sy_gx, n, h->d_S_part.p, h->d_S_sum.p);
+      k_reduce_rows<<<(n + RR_E - 1) / RR_E, RR_E * RR_S, 0, h->stream>>>(h->sy_gx, n, h->d_S_part.p, S_sum_buf(h));
     }
     CU(cudaGetLastError());
-    ST(allreduce(h, h->d_S_sum.p, n, ncclSum_));
+    if (h->peer_on) ST(peer_allreduce(h, 0, S_sum_buf(h), n));
+    else ST(allreduce(h, S_sum_buf(h), n, ncclSum_));
   }
   {
     const size_t need = ((size_t)C * (C + 1) / 2 + C + 1) * sizeof(double);   // packed lower triangle + rhs row
@@ -966,11 +1135,11 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     {
       KScope ks(h, KC_SOLVE);
       if (packed)
-        k_solve_cam<true><<<1, CH_THREADS, need, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc2[h->blk].p, h->d_gc2[h->blk].p, h->d_S_sum.p,
+        k_solve_cam<true><<<1, CH_THREADS, need, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc2[h->blk].p, h->d_gc2[h->blk].p, S_sum_buf(h),
                                                               h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
                                                               h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, h->d_fail.p);
       else
-        k_solve_cam<false><<<1, CH_THREADS, 0, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc2[h->blk].p, h->d_gc2[h->blk].p, h->d_S_sum.p,
+        k_solve_cam<false><<<1, CH_THREADS, 0, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc2[h->blk].p, h->d_gc2[h->blk].p, S_sum_buf(h),
                                                             h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
                                                             h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, h->d_fail.p);
     }
@@ -990,8 +1159,8 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     // the step's scalars are reduced first; with several ranks they (and the failure flag) go into the tail of the
     // buffer that the Jacobian pass all-reduces, so the whole iteration has two collectives: this one and K2's
     const bool multi = h->nranks > 1;
-    double* tail = h->d_cc_sum.p + h->E;
-    if (multi) CU(cudaMemsetAsync(h->d_cc_sum.p, 0, ((size_t)h->E + COMM_SCAL + 2 * 64) * sizeof(double), h->stream));
+    double* tail = cc_sum_buf(h) + h->E;
+    if (multi) CU(cudaMemsetAsync(cc_sum_buf(h), 0, ((size_t)h->E + COMM_SCAL + 2 * 64) * sizeof(double), h->stream));
     jobs.j[0] = ReduceJob{h->d_mcc_f.p, 0, multi ? tail + 3 : h->d_scal.p + 4};
     jobs.j[1] = ReduceJob{h->d_dx2_f.p, 0, multi ? tail + 4 : h->d_scal.p + 5};
     jobs.j[2] = ReduceJob{h->d_xn2c_f.p, 0, multi ? tail + 5 : h->d_scal.p + 6};
@@ -1171,6 +1340,8 @@ mcc_status mcc_create(mcc_handle** out) {
 void mcc_destroy(mcc_handle* h) {
   if (!h) return;
   if (h->device >= 0) cudaSetDevice(h->device);
+  free_peer_window(h);
+  if (h->comm && nccl().has_windows()) free_comm_windows(h);
   if (h->comm && nccl().CommDestroy) nccl().CommDestroy(h->comm);
   DBuf<double>* dd[] = {&h->d_aos_w, &h->d_aos_i, &h->d_X, &h->d_Y, &h->d_Z, &h->d_U, &h->d_V, &h->d_res, &h->d_camp[0], &h->d_camp[1], &h->d_pose[0], &h->d_pose[1],
                         &h->d_setup, &h->d_G, &h->d_tile_s, &h->d_Hff2[0], &h->d_Hff2[1], &h->d_gf2[0], &h->d_gf2[1], &h->d_Hfc2[0], &h->d_Hfc2[1], &h->d_Lf, &h->d_cost_f, &h->d_gmax_f, &h->d_xn2_f, &h->d_newcost_f,
