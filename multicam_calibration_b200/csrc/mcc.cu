@@ -414,6 +414,7 @@ mcc_status ensure_device(mcc_handle* h) {
     CU((cudaFuncSetAttribute(k_tile_normal<21, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
     CU((cudaFuncSetAttribute(k_tile_normal<20, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
     CU((cudaFuncSetAttribute(k_tile_normal<28, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
+    CU(cudaFuncSetAttribute(k_group_setup, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SETUP_SMEM_BYTES));
     CU(cudaFuncSetAttribute(k_schur_syrk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(k_schur_syrk<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CU(cudaFuncSetAttribute(k_solve_cam<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 196 * 1024));
@@ -840,7 +841,8 @@ mcc_status launch_setup(mcc_handle* h, int which) {
   if (h->ngroups == 0) return MCC_OK;
   {
     KScope ks(h, KC_SETUP);
-    k_group_setup<<<(h->ngroups + 127) / 128, 128, 0, h->stream>>>(h->ngroups, h->ncam(), h->d_cams.p, h->d_camp[which].p, h->d_pose[which].p, h->d_setup.p);
+    const int fpb = std::min(32, 128 / h->ncam());
+    k_group_setup<<<(h->nslots + fpb - 1) / fpb, 128, SETUP_SMEM_BYTES, h->stream>>>(h->nslots, h->ncam(), fpb, h->d_cams.p, h->d_camp[which].p, h->d_pose[which].p, h->d_setup.p);
   }
   CU(cudaGetLastError());
   return MCC_OK;
