@@ -1108,7 +1108,7 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
                                                                     h->d_Lf.p, h->d_Linv.p, h->d_zf.p, h->d_fail.p);
     }
     CU(cudaGetLastError());
-    const size_t smem0 = ((size_t)SY_FB * 6 * h->LD + 2 * SY_FB * (36 + 18)) * sizeof(double);
+    const size_t smem0 = std::max(((size_t)SY_FB * 6 * h->LD + 2 * SY_FB * (36 + 18)) * sizeof(double), (size_t)SY_THREADS * (SY_T * SY_T + 1) * sizeof(double));
     const size_t smem1 = smem0 + (size_t)SY_FB * 6 * C * sizeof(double);
     const bool pf = smem1 <= 112 * 1024;   // keep two CTAs per SM; wider systems read Hfc straight from global memory
     dim3 grid(h->sy_gx, h->sy_gy);
