@@ -736,6 +736,7 @@ mcc_status build_structure(mcc_handle* h) {
   CU(up(h->d_hfc_tab, hfc_tab));
   CU(up(h->d_cam_tiles, cam_tiles));
   CU(up(h->d_cc_chunks, cc_chunks));
+  cam_chunk0.insert(cam_chunk0.end(), cc_e0.begin(), cc_e0.end());   // [ncam+1] chunk ranges, then [ncam+1] entry ranges
   CU(up(h->d_cam_chunk0, cam_chunk0));
   CU(h->d_w_f.reserve(std::max(h->nslots, 1)));
   CU(h->d_Linv.reserve((size_t)std::max(h->nslots, 1) * 6)); CU(h->d_zf.reserve((size_t)std::max(h->nslots, 1) * 6));
@@ -1019,11 +1020,12 @@ mcc_status allreduce(mcc_handle* h, double* p, size_t n, int op) {
 // blocks of parameter set `which` into block set `bo`
 // Several ranks: the camera-camera entries and every scalar of the iteration travel in ONE all-reduce (sum) over
 // d_cc_sum = [entries E | 6 scalars | gradient max per rank | failure flag per rank]; k_scatter_cc unpacks it.
-// step_scalars: launch_step has already put its three sums and the failure flag into the tail (and cleared the buffer).
-mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, bool step_scalars = false) {
+// extra: further per-frame arrays to reduce in the same launch (launch_step's scalars of a speculative step).
+mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const ReduceJob* extra = nullptr, int nextra = 0) {
   const bool multi = h->nranks > 1;
   double* tail = cc_sum_buf(h) + h->E;
-  if (!step_scalars) CU(cudaMemsetAsync(cc_sum_buf(h), 0, ((size_t)h->E + COMM_SCAL + 2 * 64) * sizeof(double), h->stream));
+  // the per-rank slots of the other ranks have to be zero; on one rank every entry is written (k_reduce_misc)
+  if (multi) CU(cudaMemsetAsync(cc_sum_buf(h), 0, ((size_t)h->E + COMM_SCAL + 2 * 64) * sizeof(double), h->stream));
   ST(launch_setup(h, which));
   if (h->ntiles) {
     const size_t smem = (size_t)K1_WARPS * (k1_rows_doubles(h->rowstride) + K1_EXTRA) * sizeof(double);
@@ -1046,28 +1048,24 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, bool 
                                                      h->d_gmax_f.p, h->d_xn2_f.p, h->d_w_f.p);
   }
   CU(cudaGetLastError());
-  if (h->E) {
-    if (h->ncc_chunks) {
-      KScope ks(h, KC_ASSEMBLE);
-      k_cc_partial<<<h->ncc_chunks, 128, 0, h->stream>>>(h->ncam(), h->d_cc_chunks.p, h->d_cam_tiles.p, h->d_tiles.p, h->d_cc.p, h->d_w_f.p, h->d_G.p,
-                                                         h->gstride, h->cc_maxne, h->d_cc_part.p);
-    }
-    CU(cudaGetLastError());
-    {
-      KScope ks(h, KC_REDUCE);
-      k_cc_reduce<<<h->ncam(), 1024, (size_t)CCR_S * h->cc_maxne * sizeof(double), h->stream>>>(h->ncam(), h->d_cam_chunk0.p, h->d_cc_chunks.p, h->cc_maxne,
-                                                                                               h->d_cc_part.p, cc_sum_buf(h));
-    }
-    CU(cudaGetLastError());
+  if (h->E && h->ncc_chunks) {
+    KScope ks(h, KC_ASSEMBLE);
+    k_cc_partial<<<h->ncc_chunks, 128, 0, h->stream>>>(h->ncam(), h->d_cc_chunks.p, h->d_cam_tiles.p, h->d_tiles.p, h->d_cc.p, h->d_w_f.p, h->d_G.p,
+                                                       h->gstride, h->cc_maxne, h->d_cc_part.p);
   }
+  CU(cudaGetLastError());
   ReduceJobs jobs;
   std::memset(&jobs, 0, sizeof(jobs));
   jobs.j[0] = ReduceJob{h->d_cost_f.p, 0, multi ? tail + 0 : nullptr};
   jobs.j[1] = ReduceJob{h->d_xn2_f.p, 0, multi ? tail + 1 : nullptr};
   jobs.j[2] = ReduceJob{h->d_gmax_f.p, 1, multi ? tail + COMM_SCAL + h->rank : nullptr};
+  for (int i = 0; i < nextra && i < 5; i++) jobs.j[3 + i] = extra[i];
   {
     KScope ks(h, KC_REDUCE);
-    k_reduce_arrays<<<3, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p);
+    const int ncc = h->E ? h->ncam() : 0;
+    const size_t smem = std::max((size_t)CCR_S * h->cc_maxne, (size_t)1024) * sizeof(double);
+    k_reduce_misc<<<ncc + 3 + nextra, 1024, smem, h->stream>>>(ncc, h->ncam(), h->d_cam_chunk0.p, h->d_cc_chunks.p, h->cc_maxne, h->d_cc_part.p, cc_sum_buf(h), jobs,
+                                                               h->nslots, h->d_scal.p);
   }
   CU(cudaGetLastError());
   if (multi) {
@@ -1158,21 +1156,16 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
   ReduceJobs jobs;
   std::memset(&jobs, 0, sizeof(jobs));
   if (speculate) {
-    // the step's scalars are reduced first; with several ranks they (and the failure flag) go into the tail of the
-    // buffer that the Jacobian pass all-reduces, so the whole iteration has two collectives: this one and K2's
+    // the step's scalars are reduced in the same launch as the Jacobian pass's; with several ranks they (and the
+    // failure flag) ride in the tail of the buffer that pass all-reduces: two collectives per iteration, this and K2's
     const bool multi = h->nranks > 1;
     double* tail = cc_sum_buf(h) + h->E;
-    if (multi) CU(cudaMemsetAsync(cc_sum_buf(h), 0, ((size_t)h->E + COMM_SCAL + 2 * 64) * sizeof(double), h->stream));
-    jobs.j[0] = ReduceJob{h->d_mcc_f.p, 0, multi ? tail + 3 : h->d_scal.p + 4};
-    jobs.j[1] = ReduceJob{h->d_dx2_f.p, 0, multi ? tail + 4 : h->d_scal.p + 5};
-    jobs.j[2] = ReduceJob{h->d_xn2c_f.p, 0, multi ? tail + 5 : h->d_scal.p + 6};
-    jobs.j[3] = ReduceJob{reinterpret_cast<const double*>(h->d_fail.p), 2, tail + COMM_SCAL + h->nranks + h->rank};
-    {
-      KScope ks(h, KC_REDUCE);
-      k_reduce_arrays<<<multi ? 4 : 3, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p);
-    }
-    CU(cudaGetLastError());
-    ST(launch_jacobian(h, o.use_loss, cand, 1 - h->blk, multi));   // cost, |x|^2, gradient norm -> d_scal[0..2], [8..9]
+    ReduceJob extra[4];
+    extra[0] = ReduceJob{h->d_mcc_f.p, 0, multi ? tail + 3 : h->d_scal.p + 4};
+    extra[1] = ReduceJob{h->d_dx2_f.p, 0, multi ? tail + 4 : h->d_scal.p + 5};
+    extra[2] = ReduceJob{h->d_xn2c_f.p, 0, multi ? tail + 5 : h->d_scal.p + 6};
+    extra[3] = ReduceJob{reinterpret_cast<const double*>(h->d_fail.p), 2, tail + COMM_SCAL + h->nranks + h->rank};
+    ST(launch_jacobian(h, o.use_loss, cand, 1 - h->blk, extra, multi ? 4 : 3));   // cost, |x|^2, gradient norm -> d_scal[0..2], [8..9]
     return MCC_OK;
   }
   ST(launch_cost(h, cand, o.use_loss, h->d_newcost_f.p, nullptr));
