@@ -288,7 +288,7 @@ struct mcc_handle {
   DBuf<double> d_aos_w, d_aos_i, d_X, d_Y, d_Z, d_U, d_V, d_res;
   DBuf<uint8_t> d_mask;
   DBuf<Tile> d_tiles;
-  DBuf<int> d_gto, d_lut, d_col_param, d_fail, d_hff_tab, d_cam_tiles, d_cam_chunk0;
+  DBuf<int> d_gto, d_lut, d_col_param, d_hff_tab, d_cam_tiles, d_cam_chunk0;
   DBuf<int2> d_hfc_tab;
   DBuf<CcChunk> d_cc_chunks;
   DBuf<double> d_w_f, d_Linv, d_zf;
@@ -313,7 +313,6 @@ struct mcc_handle {
   unsigned long long peer_seq[2] = {0, 0};
   bool peer_on = false, peer_failed = false;
   double* h_scal = nullptr;            // pinned mirror of d_scal
-  int* h_fail = nullptr;
   int asm_grid = 0, sy_gx = 0, sy_gy = 0;
   int sms = 0;
   int gram_mode = 0;                   // 0: FP64 FMA 3x3 register blocks, 1: FP64 mma.sync (DMMA) 8x8 tiles
@@ -407,8 +406,7 @@ mcc_status ensure_device(mcc_handle* h) {
   if (h->device < 0) CU(cudaGetDevice(&h->device));
   CU(cudaSetDevice(h->device));
   if (!h->stream) CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-  if (!h->h_scal) CU(cudaHostAlloc((void**)&h->h_scal, 32 * sizeof(double), cudaHostAllocDefault));
-  if (!h->h_fail) CU(cudaHostAlloc((void**)&h->h_fail, sizeof(int), cudaHostAllocDefault));
+  if (!h->h_scal) CU(cudaHostAlloc((void**)&h->h_scal, 33 * sizeof(double), cudaHostAllocDefault));
   if (!h->attrs_set) {
     CU((cudaFuncSetAttribute(k_tile_normal<15, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
     CU((cudaFuncSetAttribute(k_tile_normal<21, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
@@ -756,7 +754,7 @@ mcc_status build_structure(mcc_handle* h) {
   CU(h->d_scale_c.reserve(std::max(C, 1))); CU(h->d_scale_f.reserve(ns * 6));
   CU(h->d_S_part.reserve((size_t)h->sy_gx * h->npairs * SY_T * SY_T)); CU(h->d_S_sum.reserve((size_t)h->npairs * SY_T * SY_T));
   CU(h->d_M.reserve((size_t)(C + 1) * std::max(C, 1))); CU(h->d_yc.reserve(std::max(C, 1))); CU(h->d_ysc.reserve(std::max(C, 1)));
-  CU(h->d_scal.reserve(32)); CU(h->d_fail.reserve(1));
+  CU(h->d_scal.reserve(40));   // 32 scalars + the failure flags (an int at [32]) so that one copy brings both back
   for (int i = 0; i < 2; i++) { CU(h->d_camp[i].reserve(std::max(h->C_full, 1))); CU(h->d_pose[i].reserve(ns * 6)); }
   CU(cudaStreamSynchronize(h->stream));   // the staging vectors above die with this scope
   h->structure_dirty = false;
@@ -871,6 +869,7 @@ mcc_status launch_cost(mcc_handle* h, int which, int use_loss, double* cost_f_ou
   return MCC_OK;
 }
 
+inline int* fail_ptr(mcc_handle* h) { return reinterpret_cast<int*>(h->d_scal.p + 32); }
 inline double* S_sum_buf(mcc_handle* h) { return h->win_S ? h->win_S : h->d_S_sum.p; }
 inline double* cc_sum_buf(mcc_handle* h) { return h->win_cc ? h->win_cc : h->d_cc_sum.p; }
 
@@ -916,7 +915,7 @@ void free_peer_window(mcc_handle* h) {
   if (!h->peer_own) return;
   cudaStreamSynchronize(h->stream);
   if (h->comm) {   // nobody may still be storing into a window that is about to go away
-    nccl().AllReduce(h->d_fail.p, h->d_fail.p, 1, ncclInt32_, ncclMax_, h->comm, h->stream);
+    nccl().AllReduce(fail_ptr(h), fail_ptr(h), 1, ncclInt32_, ncclMax_, h->comm, h->stream);
     cudaStreamSynchronize(h->stream);
   }
   for (int r = 0; r < h->pw.nranks; r++)
@@ -1005,7 +1004,7 @@ mcc_status peer_allreduce(mcc_handle* h, int ex, double* p, size_t n) {
   const size_t off = base + (seq & 1) * (size_t)R * slot_n;
   // the sequence number in the cells is 32 bits and never 0 (0 = a fresh window)
   const unsigned int seq32 = (unsigned int)(seq % 0xffffffffull) + 1u;
-  k_peer_allreduce<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->pw, p, (int)n, off, seq32, h->d_fail.p);
+  k_peer_allreduce<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->pw, p, (int)n, off, seq32, fail_ptr(h));
   CU(cudaGetLastError());
   return MCC_OK;
 }
@@ -1076,17 +1075,16 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
   {
     KScope ks(h, KC_REDUCE);
     k_scatter_cc<<<1, 1024, 0, h->stream>>>(h->C, h->E, h->d_cc.p, cc_sum_buf(h), h->d_col_param.p, h->d_camp[which].p, h->d_Hcc2[bo].p, h->d_gc2[bo].p, h->d_scal.p + 8,
-                                             h->nranks, h->d_scal.p, h->d_fail.p);
+                                             h->nranks, h->d_scal.p, fail_ptr(h));
   }
   CU(cudaGetLastError());
   return MCC_OK;
 }
 
 mcc_status read_scalars(mcc_handle* h) {
-  CU(cudaMemcpyAsync(h->h_scal, h->d_scal.p, 32 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-  CU(cudaMemcpyAsync(h->h_fail, h->d_fail.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaMemcpyAsync(h->h_scal, h->d_scal.p, 33 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));   // scalars + failure flags
   CU(cudaStreamSynchronize(h->stream));
-  h->d2h += 32 * sizeof(double) + sizeof(int);
+  h->d2h += 33 * sizeof(double);
   if (h->ktiming) resolve_ktiming(h);
   return MCC_OK;
 }
@@ -1098,12 +1096,12 @@ mcc_status read_scalars(mcc_handle* h) {
 mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool speculate) {
   const int cur = h->cur, cand = 1 - cur;
   const int C = h->C;
-  CU(cudaMemsetAsync(h->d_fail.p, 0, sizeof(int), h->stream));
+  CU(cudaMemsetAsync(fail_ptr(h), 0, sizeof(int), h->stream));
   {
     if (h->nslots) {
       KScope ks(h, KC_SCHUR);
       k_frame_chol<<<(h->nslots + 127) / 128, 128, 0, h->stream>>>(h->nslots, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hff2[h->blk].p, h->d_gf2[h->blk].p, h->d_scale_f.p,
-                                                                    h->d_Lf.p, h->d_Linv.p, h->d_zf.p, h->d_fail.p);
+                                                                    h->d_Lf.p, h->d_Linv.p, h->d_zf.p, fail_ptr(h));
     }
     CU(cudaGetLastError());
     const size_t smem0 = std::max(((size_t)SY_FB * 6 * h->LD + 2 * SY_FB * (36 + 18)) * sizeof(double), (size_t)SY_THREADS * (SY_T * SY_T + 1) * sizeof(double));
@@ -1137,11 +1135,11 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
       if (packed)
         k_solve_cam<true><<<1, CH_THREADS, need, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc2[h->blk].p, h->d_gc2[h->blk].p, S_sum_buf(h),
                                                               h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
-                                                              h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, h->d_fail.p);
+                                                              h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, fail_ptr(h));
       else
         k_solve_cam<false><<<1, CH_THREADS, 0, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc2[h->blk].p, h->d_gc2[h->blk].p, S_sum_buf(h),
                                                             h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
-                                                            h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, h->d_fail.p);
+                                                            h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, fail_ptr(h));
     }
     CU(cudaGetLastError());
   }
@@ -1149,7 +1147,7 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     {
       KScope ks(h, KC_BACKSUB);
       k_backsub<<<(h->nslots + 3) / 4, 128, 0, h->stream>>>(h->nslots, C, h->d_Hff2[h->blk].p, h->d_gf2[h->blk].p, h->d_Hfc2[h->blk].p, h->d_Lf.p, h->d_scale_f.p, h->d_ysc.p,
-                                                         h->d_pose[cur].p, h->d_pose[cand].p, h->d_mcc_f.p, h->d_dx2_f.p, h->d_xn2c_f.p, h->d_fail.p);
+                                                         h->d_pose[cur].p, h->d_pose[cand].p, h->d_mcc_f.p, h->d_dx2_f.p, h->d_xn2c_f.p, fail_ptr(h));
     }
     CU(cudaGetLastError());
   }
@@ -1164,7 +1162,7 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     extra[0] = ReduceJob{h->d_mcc_f.p, 0, multi ? tail + 3 : h->d_scal.p + 4};
     extra[1] = ReduceJob{h->d_dx2_f.p, 0, multi ? tail + 4 : h->d_scal.p + 5};
     extra[2] = ReduceJob{h->d_xn2c_f.p, 0, multi ? tail + 5 : h->d_scal.p + 6};
-    extra[3] = ReduceJob{reinterpret_cast<const double*>(h->d_fail.p), 2, tail + COMM_SCAL + h->nranks + h->rank};
+    extra[3] = ReduceJob{reinterpret_cast<const double*>(fail_ptr(h)), 2, tail + COMM_SCAL + h->nranks + h->rank};
     ST(launch_jacobian(h, o.use_loss, cand, 1 - h->blk, extra, multi ? 4 : 3));   // cost, |x|^2, gradient norm -> d_scal[0..2], [8..9]
     return MCC_OK;
   }
@@ -1181,7 +1179,7 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
   if (h->nranks > 1) {
     NC(nccl().GroupStart());
     ST(allreduce(h, h->d_scal.p + 3, 4, ncclSum_));
-    NC(nccl().AllReduce(h->d_fail.p, h->d_fail.p, 1, ncclInt32_, ncclMax_, h->comm, h->stream));
+    NC(nccl().AllReduce(fail_ptr(h), fail_ptr(h), 1, ncclInt32_, ncclMax_, h->comm, h->stream));
     NC(nccl().GroupEnd());
   }
   return MCC_OK;
@@ -1243,7 +1241,7 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
     ST(read_scalars(h));
     S.t_linear += now_s() - t0; S.n_linear_solves++;
     if (spec) S.n_jacobian_evals++; else S.n_residual_evals++;
-    const int flags = *h->h_fail;
+    const int flags = *reinterpret_cast<const int*>(h->h_scal + 32);
     const double new_cost = spec ? h->h_scal[0] : h->h_scal[3];
     const double mcc = h->h_scal[4] + h->h_scal[10];
     const double step_norm = std::sqrt(h->h_scal[5] + h->h_scal[11]);
@@ -1343,12 +1341,11 @@ void mcc_destroy(mcc_handle* h) {
                         &h->d_mcc_f, &h->d_dx2_f, &h->d_xn2c_f, &h->d_cc_part, &h->d_cc_sum, &h->d_Hcc2[0], &h->d_Hcc2[1], &h->d_gc2[0], &h->d_gc2[1], &h->d_scale_c, &h->d_scale_f, &h->d_S_part,
                         &h->d_S_sum, &h->d_M, &h->d_yc, &h->d_ysc, &h->d_scal};
   for (auto* b : dd) b->release();
-  h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_lut.release(); h->d_col_param.release(); h->d_fail.release();
+  h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_lut.release(); h->d_col_param.release(); 
   h->d_cams.release(); h->d_cc.release(); h->d_colmap.release(); h->d_hff_tab.release(); h->d_hfc_tab.release();
   h->d_cam_tiles.release(); h->d_cam_chunk0.release(); h->d_cc_chunks.release(); h->d_w_f.release(); h->d_Linv.release(); h->d_zf.release();
   h->world.release(); h->image.release();
   if (h->h_scal) cudaFreeHost(h->h_scal);
-  if (h->h_fail) cudaFreeHost(h->h_fail);
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   for (KPending& pe : h->ev_pending) { cudaEventDestroy(pe.a); cudaEventDestroy(pe.b); }
   if (h->tm_a) { cudaEventDestroy(h->tm_a); cudaEventDestroy(h->tm_b); }
