@@ -312,6 +312,16 @@ struct mcc_handle {
   size_t peer_nS = 0, peer_nC = 0;      // slot sizes the window was laid out for
   unsigned long long peer_seq[2] = {0, 0};
   bool peer_on = false, peer_failed = false;
+  // iterations queued ahead of their accept / reject decision (solve(): pipelined section)
+  LmState* d_state = nullptr;
+  const LmState* st_cur = nullptr;      // what every launch passes: d_state while the pipeline runs, else nullptr
+  double* d_rec = nullptr;              // [2][LM_REC] decision records
+  double* h_rec = nullptr;              // pinned mirror
+  cudaEvent_t ev_rec[2] = {nullptr, nullptr};
+  // one captured CUDA graph per (parameter set, block set, record slot) of a queued iteration; rebuilt when the
+  // structure or the options change (single rank only: the peer exchange takes a new sequence number per launch)
+  cudaGraphExec_t it_graph[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  double it_graph_key[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};   // the option values baked into the graphs
   double* h_scal = nullptr;            // pinned mirror of d_scal
   int asm_grid = 0, sy_gx = 0, sy_gy = 0;
   int sms = 0;
@@ -407,6 +417,12 @@ mcc_status ensure_device(mcc_handle* h) {
   CU(cudaSetDevice(h->device));
   if (!h->stream) CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   if (!h->h_scal) CU(cudaHostAlloc((void**)&h->h_scal, 33 * sizeof(double), cudaHostAllocDefault));
+  if (!h->d_state) {
+    CU(cudaMalloc((void**)&h->d_state, sizeof(LmState)));
+    CU(cudaMalloc((void**)&h->d_rec, 2 * LM_REC * sizeof(double)));
+    CU(cudaHostAlloc((void**)&h->h_rec, 2 * LM_REC * sizeof(double), cudaHostAllocDefault));
+    for (int i = 0; i < 2; i++) CU(cudaEventCreateWithFlags(&h->ev_rec[i], cudaEventDisableTiming));
+  }
   if (!h->attrs_set) {
     CU((cudaFuncSetAttribute(k_tile_normal<15, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
     CU((cudaFuncSetAttribute(k_tile_normal<21, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
@@ -450,6 +466,10 @@ int tri_index(int bi, int bj, int nb) { return bi * nb - bi * (bi - 1) / 2 + (bj
 
 // Everything that depends on cameras, flags, frame list and masks: reduced column maps
 // (calibrator.cpp:510-521), frames with residual blocks (calibrator.cpp:482-485), tiles.
+void drop_iteration_graphs(mcc_handle* h) {
+  for (cudaGraphExec_t& g : h->it_graph) { if (g) cudaGraphExecDestroy(g); g = nullptr; }
+}
+
 // Lane -> (unit, slice) map of the K1 contraction.  A 64-bit shared load is served one half-warp at a time, so the map
 // is searched (backtracking, bounded) for one where the <= 16 lanes of each half-warp hit different 8-byte banks for
 // the unit's own block column and for every partner column; slice q reads rows q, q + ksl, ... and the row stride rs
@@ -759,6 +779,7 @@ mcc_status build_structure(mcc_handle* h) {
   CU(cudaStreamSynchronize(h->stream));   // the staging vectors above die with this scope
   h->structure_dirty = false;
   h->params_dirty = true;
+  drop_iteration_graphs(h);
   return MCC_OK;
 }
 
@@ -841,7 +862,7 @@ mcc_status launch_setup(mcc_handle* h, int which) {
   {
     KScope ks(h, KC_SETUP);
     const int fpb = std::min(32, 128 / h->ncam());
-    k_group_setup<<<(h->nslots + fpb - 1) / fpb, 128, SETUP_SMEM_BYTES, h->stream>>>(h->nslots, h->ncam(), fpb, h->d_cams.p, h->d_camp[which].p, h->d_pose[which].p, h->d_setup.p);
+    k_group_setup<<<(h->nslots + fpb - 1) / fpb, 128, SETUP_SMEM_BYTES, h->stream>>>(h->nslots, h->ncam(), fpb, h->d_cams.p, h->d_camp[which].p, h->d_pose[which].p, h->d_setup.p, h->st_cur);
   }
   CU(cudaGetLastError());
   return MCC_OK;
@@ -1004,7 +1025,7 @@ mcc_status peer_allreduce(mcc_handle* h, int ex, double* p, size_t n) {
   const size_t off = base + (seq & 1) * (size_t)R * slot_n;
   // the sequence number in the cells is 32 bits and never 0 (0 = a fresh window)
   const unsigned int seq32 = (unsigned int)(seq % 0xffffffffull) + 1u;
-  k_peer_allreduce<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->pw, p, (int)n, off, seq32, fail_ptr(h));
+  k_peer_allreduce<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->pw, p, (int)n, off, seq32, fail_ptr(h), h->st_cur);
   CU(cudaGetLastError());
   return MCC_OK;
 }
@@ -1032,7 +1053,7 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
     KScope ks(h, KC_TILE_NORMAL);
 #define MCC_LAUNCH_TILE_NORMAL(RS, MMA)                                                                                                     \
     k_tile_normal<RS, MMA><<<grid, K1_WARPS * 32, smem, h->stream>>>(h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, \
-                                                                      h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p, h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p)
+                                                                      h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p, h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p, h->st_cur)
     if (h->rowstride == 15) MCC_LAUNCH_TILE_NORMAL(15, false);
     else if (h->rowstride == 21) MCC_LAUNCH_TILE_NORMAL(21, false);
     else if (h->rowstride == 20) MCC_LAUNCH_TILE_NORMAL(20, true);
@@ -1044,13 +1065,13 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
     KScope ks(h, KC_ASSEMBLE);
     k_frame_blocks<<<h->nslots, 128, 0, h->stream>>>(h->nslots, h->ncam(), h->C, h->d_gto.p, h->d_hff_tab.p, h->d_hfc_tab.p, h->d_G.p, h->gstride,
                                                      h->d_tile_s.p, h->d_pose[which].p, use_loss, h->d_Hff2[bo].p, h->d_gf2[bo].p, h->d_Hfc2[bo].p, h->d_cost_f.p,
-                                                     h->d_gmax_f.p, h->d_xn2_f.p, h->d_w_f.p);
+                                                     h->d_gmax_f.p, h->d_xn2_f.p, h->d_w_f.p, h->st_cur);
   }
   CU(cudaGetLastError());
   if (h->E && h->ncc_chunks) {
     KScope ks(h, KC_ASSEMBLE);
     k_cc_partial<<<h->ncc_chunks, 128, 0, h->stream>>>(h->ncam(), h->d_cc_chunks.p, h->d_cam_tiles.p, h->d_tiles.p, h->d_cc.p, h->d_w_f.p, h->d_G.p,
-                                                       h->gstride, h->cc_maxne, h->d_cc_part.p);
+                                                       h->gstride, h->cc_maxne, h->d_cc_part.p, h->st_cur);
   }
   CU(cudaGetLastError());
   ReduceJobs jobs;
@@ -1064,7 +1085,7 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
     const int ncc = h->E ? h->ncam() : 0;
     const size_t smem = std::max((size_t)CCR_S * h->cc_maxne, (size_t)1024) * sizeof(double);
     k_reduce_misc<<<ncc + 3 + nextra, 1024, smem, h->stream>>>(ncc, h->ncam(), h->d_cam_chunk0.p, h->d_cc_chunks.p, h->cc_maxne, h->d_cc_part.p, cc_sum_buf(h), jobs,
-                                                               h->nslots, h->d_scal.p);
+                                                               h->nslots, h->d_scal.p, h->st_cur);
   }
   CU(cudaGetLastError());
   if (multi) {
@@ -1075,7 +1096,7 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
   {
     KScope ks(h, KC_REDUCE);
     k_scatter_cc<<<1, 1024, 0, h->stream>>>(h->C, h->E, h->d_cc.p, cc_sum_buf(h), h->d_col_param.p, h->d_camp[which].p, h->d_Hcc2[bo].p, h->d_gc2[bo].p, h->d_scal.p + 8,
-                                             h->nranks, h->d_scal.p, fail_ptr(h));
+                                             h->nranks, h->d_scal.p, fail_ptr(h), h->st_cur);
   }
   CU(cudaGetLastError());
   return MCC_OK;
@@ -1101,7 +1122,7 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     if (h->nslots) {
       KScope ks(h, KC_SCHUR);
       k_frame_chol<<<(h->nslots + 127) / 128, 128, 0, h->stream>>>(h->nslots, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hff2[h->blk].p, h->d_gf2[h->blk].p, h->d_scale_f.p,
-                                                                    h->d_Lf.p, h->d_Linv.p, h->d_zf.p, fail_ptr(h));
+                                                                    h->d_Lf.p, h->d_Linv.p, h->d_zf.p, fail_ptr(h), h->st_cur);
     }
     CU(cudaGetLastError());
     const size_t smem0 = std::max(((size_t)SY_FB * 6 * h->LD + 2 * SY_FB * (36 + 18)) * sizeof(double), (size_t)SY_THREADS * (SY_T * SY_T + 1) * sizeof(double));
@@ -1112,16 +1133,16 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
       KScope ks(h, KC_SCHUR);
       if (pf)
         k_schur_syrk<true><<<grid, SY_THREADS, smem1, h->stream>>>(h->nslots, C, h->LD, h->npairs, h->d_Hfc2[h->blk].p, h->d_scale_f.p, h->d_scale_c.p, h->d_Lf.p,
-                                                                   h->d_Linv.p, h->d_zf.p, h->d_S_part.p);
+                                                                   h->d_Linv.p, h->d_zf.p, h->d_S_part.p, h->st_cur);
       else
         k_schur_syrk<false><<<grid, SY_THREADS, smem0, h->stream>>>(h->nslots, C, h->LD, h->npairs, h->d_Hfc2[h->blk].p, h->d_scale_f.p, h->d_scale_c.p, h->d_Lf.p,
-                                                                    h->d_Linv.p, h->d_zf.p, h->d_S_part.p);
+                                                                    h->d_Linv.p, h->d_zf.p, h->d_S_part.p, h->st_cur);
     }
     CU(cudaGetLastError());
     const int n = h->npairs * SY_T * SY_T;
     {
       KScope ks(h, KC_REDUCE);
-      k_reduce_rows<<<(n + RR_E - 1) / RR_E, RR_E * RR_S, 0, h->stream>>>(h->sy_gx, n, h->d_S_part.p, S_sum_buf(h));
+      k_reduce_rows<<<(n + RR_E - 1) / RR_E, RR_E * RR_S, 0, h->stream>>>(h->sy_gx, n, h->d_S_part.p, S_sum_buf(h), h->st_cur);
     }
     CU(cudaGetLastError());
     if (h->peer_on) ST(peer_allreduce(h, 0, S_sum_buf(h), n));
@@ -1135,11 +1156,11 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
       if (packed)
         k_solve_cam<true><<<1, CH_THREADS, need, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc2[h->blk].p, h->d_gc2[h->blk].p, S_sum_buf(h),
                                                               h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
-                                                              h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, fail_ptr(h));
+                                                              h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, fail_ptr(h), h->st_cur);
       else
         k_solve_cam<false><<<1, CH_THREADS, 0, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc2[h->blk].p, h->d_gc2[h->blk].p, S_sum_buf(h),
                                                             h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
-                                                            h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, fail_ptr(h));
+                                                            h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, fail_ptr(h), h->st_cur);
     }
     CU(cudaGetLastError());
   }
@@ -1147,7 +1168,7 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     {
       KScope ks(h, KC_BACKSUB);
       k_backsub<<<(h->nslots + 3) / 4, 128, 0, h->stream>>>(h->nslots, C, h->d_Hff2[h->blk].p, h->d_gf2[h->blk].p, h->d_Hfc2[h->blk].p, h->d_Lf.p, h->d_scale_f.p, h->d_ysc.p,
-                                                         h->d_pose[cur].p, h->d_pose[cand].p, h->d_mcc_f.p, h->d_dx2_f.p, h->d_xn2c_f.p, fail_ptr(h));
+                                                         h->d_pose[cur].p, h->d_pose[cand].p, h->d_mcc_f.p, h->d_dx2_f.p, h->d_xn2c_f.p, fail_ptr(h), h->st_cur);
     }
     CU(cudaGetLastError());
   }
@@ -1232,13 +1253,98 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
   // pass first (Ceres' order), and the Jacobian pass follows only on acceptance.
   bool speculate = true;
   int invalid_run = 0, iter = 0;
+  // Pipelined section: while steps are being accepted, iteration i+1 is queued before the host has seen the decision
+  // of iteration i.  k_decide takes that decision on the device (same tests as below); if it is anything but
+  // "accepted, go on" it sets a stop flag that turns the already queued iteration into no-ops, and the host picks
+  // up from the scalars of the deciding iteration with the ordinary code below.  The device keeps the radius, so the
+  // GPU never waits for the host between accepted iterations (MCC_PIPELINE=0: always the ordinary path).
+  const char* pipe_env = std::getenv("MCC_PIPELINE");
+  const bool pipeline = !(pipe_env && pipe_env[0] == '0') && !h->ktiming;
+  const char* graph_env = std::getenv("MCC_GRAPHS");
+  const bool use_graphs = pipeline && h->nranks == 1 && !(graph_env && graph_env[0] == '0');
+  if (use_graphs) {
+    const double key[9] = {o.function_tolerance, o.parameter_tolerance, o.gradient_tolerance, o.max_trust_region_radius, o.min_relative_decrease,
+                           o.min_lm_diagonal, o.max_lm_diagonal, (double)o.use_loss, 1.0};
+    if (std::memcmp(h->it_graph_key, key, sizeof(key)) != 0) { drop_iteration_graphs(h); std::memcpy(h->it_graph_key, key, sizeof(key)); }
+  }
   while (true) {
     if (iter >= o.max_num_iterations) return finish(1, 3, iter);
-    iter++;
+    bool have_scalars = false;
     t0 = now_s();
+    if (speculate && pipeline) {
+      LmState st0;
+      st0.radius = radius; st0.cost = cost; st0.x_norm = x_norm; st0.gmax = gmax; st0.stop = 0; st0.pad = 0;
+      CU(cudaMemcpyAsync(h->d_state, &st0, sizeof(st0), cudaMemcpyHostToDevice, h->stream));
+      int ecur = h->cur, eblk = h->blk, queued = 0, decided = 0;
+      auto enqueue = [&]() -> mcc_status {
+        const int slot = queued & 1;
+        auto body = [&]() -> mcc_status {
+          const int ccur = h->cur, cblk = h->blk;
+          h->cur = ecur; h->blk = eblk; h->st_cur = h->d_state;
+          mcc_status r = launch_step(h, o, radius, true);
+          h->cur = ccur; h->blk = cblk; h->st_cur = nullptr;
+          ST(r);
+          k_decide<<<1, 32, 0, h->stream>>>(h->d_state, h->d_scal.p, o.parameter_tolerance, o.function_tolerance, o.gradient_tolerance,
+                                             o.min_relative_decrease, o.max_trust_region_radius, h->d_rec + slot * LM_REC);
+          CU(cudaGetLastError());
+          CU(cudaMemcpyAsync(h->h_rec + slot * LM_REC, h->d_rec + slot * LM_REC, LM_REC * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+          return MCC_OK;
+        };
+        if (use_graphs) {
+          cudaGraphExec_t& ge = h->it_graph[(ecur << 2) | (eblk << 1) | slot];
+          if (!ge) {
+            CU(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+            const mcc_status r = body();
+            cudaGraph_t g = nullptr;
+            const cudaError_t ce = cudaStreamEndCapture(h->stream, &g);
+            if (r != MCC_OK) { if (g) cudaGraphDestroy(g); return r; }
+            CU(ce);
+            const cudaError_t ie = cudaGraphInstantiate(&ge, g, 0);
+            cudaGraphDestroy(g);
+            CU(ie);
+          }
+          CU(cudaGraphLaunch(ge, h->stream));
+        } else {
+          ST(body());
+        }
+        CU(cudaEventRecord(h->ev_rec[slot], h->stream));
+        h->d2h += LM_REC * sizeof(double);
+        ecur ^= 1; eblk ^= 1; queued++;
+        return MCC_OK;
+      };
+      while (true) {
+        while (queued - decided < 2 && iter + (queued - decided) < o.max_num_iterations) ST(enqueue());
+        if (queued == decided) break;   // iteration limit
+        const int slot = decided & 1;
+        CU(cudaEventSynchronize(h->ev_rec[slot]));
+        const double* rec = h->h_rec + slot * LM_REC;
+        decided++;
+        const int outcome = (int)rec[33];
+        if (outcome != LM_ACCEPT) {
+          // the iteration that stopped the pipeline: hand its scalars to the ordinary code (what is queued behind it does nothing)
+          CU(cudaStreamSynchronize(h->stream));
+          std::memcpy(h->h_scal, rec, 33 * sizeof(double));
+          have_scalars = true;
+          break;
+        }
+        iter++;
+        S.t_linear += now_s() - t0; t0 = now_s();
+        S.n_linear_solves++; S.n_jacobian_evals++;
+        invalid_run = 0;
+        h->cur = 1 - h->cur; h->blk = 1 - h->blk;
+        x_norm = rec[38]; radius = rec[34]; cost = rec[39]; gmax = rec[40];
+        decrease_factor = 2.0;
+        S.num_successful++;
+        log_row(cost, rec[36], gmax, rec[37], rec[35], radius);
+      }
+      if (!have_scalars) continue;      // iteration limit reached inside the pipeline: the test at the top ends the solve
+    }
+    iter++;
     const bool spec = speculate;
-    ST(launch_step(h, o, radius, spec));
-    ST(read_scalars(h));
+    if (!have_scalars) {
+      ST(launch_step(h, o, radius, spec));
+      ST(read_scalars(h));
+    }
     S.t_linear += now_s() - t0; S.n_linear_solves++;
     if (spec) S.n_jacobian_evals++; else S.n_residual_evals++;
     const int flags = *reinterpret_cast<const int*>(h->h_scal + 32);
@@ -1346,6 +1452,8 @@ void mcc_destroy(mcc_handle* h) {
   h->d_cam_tiles.release(); h->d_cam_chunk0.release(); h->d_cc_chunks.release(); h->d_w_f.release(); h->d_Linv.release(); h->d_zf.release();
   h->world.release(); h->image.release();
   if (h->h_scal) cudaFreeHost(h->h_scal);
+  drop_iteration_graphs(h);
+  if (h->d_state) { cudaFree(h->d_state); cudaFree(h->d_rec); cudaFreeHost(h->h_rec); for (int i = 0; i < 2; i++) cudaEventDestroy(h->ev_rec[i]); }
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   for (KPending& pe : h->ev_pending) { cudaEventDestroy(pe.a); cudaEventDestroy(pe.b); }
   if (h->tm_a) { cudaEventDestroy(h->tm_a); cudaEventDestroy(h->tm_b); }
