@@ -1018,14 +1018,15 @@ mcc_status ensure_peer_window(mcc_handle* h) {
 // exchange 0: Schur tile pairs (n = peer_nS), exchange 1: camera-camera entries + scalars (n <= peer_nC)
 mcc_status peer_allreduce(mcc_handle* h, int ex, double* p, size_t n) {
   const int R = h->nranks;
-  const unsigned long long seq = ++h->peer_seq[ex];
+  // queued iterations (st_cur set): the device state carries the sequence numbers, the host mirrors them from the records
+  const unsigned long long seq = h->st_cur ? h->peer_seq[ex] + 1 : ++h->peer_seq[ex];
   const size_t slot_n = ex == 0 ? h->peer_nS : h->peer_nC;
   if (n > slot_n) return fail(h, MCC_ERR_NCCL, "peer window laid out for another size");
   const size_t base = ex == 0 ? 0 : 2 * (size_t)R * h->peer_nS;
   const size_t off = base + (seq & 1) * (size_t)R * slot_n;
   // the sequence number in the cells is 32 bits and never 0 (0 = a fresh window)
   const unsigned int seq32 = (unsigned int)(seq % 0xffffffffull) + 1u;
-  k_peer_allreduce<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->pw, p, (int)n, off, seq32, fail_ptr(h), h->st_cur);
+  k_peer_allreduce<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->pw, p, (int)n, off, seq32, ex, base, slot_n, fail_ptr(h), h->st_cur);
   CU(cudaGetLastError());
   return MCC_OK;
 }
@@ -1261,7 +1262,7 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
   const char* pipe_env = std::getenv("MCC_PIPELINE");
   const bool pipeline = !(pipe_env && pipe_env[0] == '0') && !h->ktiming;
   const char* graph_env = std::getenv("MCC_GRAPHS");
-  const bool use_graphs = pipeline && h->nranks == 1 && !(graph_env && graph_env[0] == '0');
+  const bool use_graphs = pipeline && (h->nranks == 1 || h->peer_on) && !(graph_env && graph_env[0] == '0');
   if (use_graphs) {
     const double key[9] = {o.function_tolerance, o.parameter_tolerance, o.gradient_tolerance, o.max_trust_region_radius, o.min_relative_decrease,
                            o.min_lm_diagonal, o.max_lm_diagonal, (double)o.use_loss, 1.0};
@@ -1274,6 +1275,7 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
     if (speculate && pipeline) {
       LmState st0;
       st0.radius = radius; st0.cost = cost; st0.x_norm = x_norm; st0.gmax = gmax; st0.stop = 0; st0.pad = 0;
+      st0.seq[0] = h->peer_seq[0]; st0.seq[1] = h->peer_seq[1];
       CU(cudaMemcpyAsync(h->d_state, &st0, sizeof(st0), cudaMemcpyHostToDevice, h->stream));
       int ecur = h->cur, eblk = h->blk, queued = 0, decided = 0;
       auto enqueue = [&]() -> mcc_status {
@@ -1320,6 +1322,7 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
         const double* rec = h->h_rec + slot * LM_REC;
         decided++;
         const int outcome = (int)rec[33];
+        if (outcome != LM_SKIPPED) { h->peer_seq[0]++; h->peer_seq[1]++; }   // this iteration ran both exchanges
         if (outcome != LM_ACCEPT) {
           // the iteration that stopped the pipeline: hand its scalars to the ordinary code (what is queued behind it does nothing)
           CU(cudaStreamSynchronize(h->stream));
