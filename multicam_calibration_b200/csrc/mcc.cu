@@ -321,6 +321,7 @@ struct mcc_handle {
   // one captured CUDA graph per (parameter set, block set, record slot) of a queued iteration; rebuilt when the
   // structure or the options change (single rank only: the peer exchange takes a new sequence number per launch)
   cudaGraphExec_t it_graph[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  long long it_graph_kernels[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // kernels inside each graph, for the launch count
   double it_graph_key[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};   // the option values baked into the graphs
   double* h_scal = nullptr;            // pinned mirror of d_scal
   int asm_grid = 0, sy_gx = 0, sy_gy = 0;
@@ -1286,17 +1287,24 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
           mcc_status r = launch_step(h, o, radius, true);
           h->cur = ccur; h->blk = cblk; h->st_cur = nullptr;
           ST(r);
-          k_decide<<<1, 32, 0, h->stream>>>(h->d_state, h->d_scal.p, o.parameter_tolerance, o.function_tolerance, o.gradient_tolerance,
-                                             o.min_relative_decrease, o.max_trust_region_radius, h->d_rec + slot * LM_REC);
+          {
+            KScope ks(h, KC_OTHER);
+            k_decide<<<1, 32, 0, h->stream>>>(h->d_state, h->d_scal.p, o.parameter_tolerance, o.function_tolerance, o.gradient_tolerance,
+                                               o.min_relative_decrease, o.max_trust_region_radius, h->d_rec + slot * LM_REC);
+          }
           CU(cudaGetLastError());
           CU(cudaMemcpyAsync(h->h_rec + slot * LM_REC, h->d_rec + slot * LM_REC, LM_REC * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
           return MCC_OK;
         };
         if (use_graphs) {
-          cudaGraphExec_t& ge = h->it_graph[(ecur << 2) | (eblk << 1) | slot];
+          const int gi = (ecur << 2) | (eblk << 1) | slot;
+          cudaGraphExec_t& ge = h->it_graph[gi];
           if (!ge) {
+            const long long l0 = h->launches;
             CU(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
             const mcc_status r = body();
+            h->it_graph_kernels[gi] = h->launches - l0;   // captured, not launched
+            h->launches = l0;
             cudaGraph_t g = nullptr;
             const cudaError_t ce = cudaStreamEndCapture(h->stream, &g);
             if (r != MCC_OK) { if (g) cudaGraphDestroy(g); return r; }
@@ -1306,6 +1314,7 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
             CU(ie);
           }
           CU(cudaGraphLaunch(ge, h->stream));
+          h->launches += h->it_graph_kernels[gi];
         } else {
           ST(body());
         }
