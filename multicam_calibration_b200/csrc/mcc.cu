@@ -546,6 +546,15 @@ static void build_lane_map(CamMeta& m, int rs) {
   }
   m.mfin = mm;
   if (mm == 3) for (int u = 0; u < nun; u++) { m.fin_src[0][lane_of[u][0]] = (int8_t)lane_of[u][1]; m.fin_src[1][lane_of[u][0]] = (int8_t)lane_of[u][2]; }
+  for (int l = 0; l < 32; l++) {
+    int8_t b[16];
+    std::memset(b, 0, sizeof(b));
+    b[0] = m.lane_u[l]; b[1] = m.lane_q[l];
+    for (int d = 0; d < 3; d++) b[2 + d] = m.lane_u[l] >= 0 ? m.unit_o[d][m.lane_u[l]] : (int8_t)-1;
+    for (int r = 0; r < 3; r++) b[5 + r] = m.red_src[r][l];
+    b[8] = m.fin_src[0][l]; b[9] = m.fin_src[1][l];
+    std::memcpy(&m.lane_info[l], b, 16);
+  }
 }
 
 mcc_status build_structure(mcc_handle* h) {
