@@ -314,6 +314,7 @@ struct mcc_handle {
   bool peer_on = false, peer_failed = false;
   // iterations queued ahead of their accept / reject decision (solve(): pipelined section)
   LmState* d_state = nullptr;
+  unsigned int* d_ticket = nullptr;     // tile counter of k_tile_normal's persistent warps
   const LmState* st_cur = nullptr;      // what every launch passes: d_state while the pipeline runs, else nullptr
   double* d_rec = nullptr;              // [2][LM_REC] decision records
   double* h_rec = nullptr;              // pinned mirror
@@ -420,6 +421,7 @@ mcc_status ensure_device(mcc_handle* h) {
   if (!h->h_scal) CU(cudaHostAlloc((void**)&h->h_scal, 33 * sizeof(double), cudaHostAllocDefault));
   if (!h->d_state) {
     CU(cudaMalloc((void**)&h->d_state, sizeof(LmState)));
+    CU(cudaMalloc((void**)&h->d_ticket, sizeof(unsigned int)));
     CU(cudaMalloc((void**)&h->d_rec, 2 * LM_REC * sizeof(double)));
     CU(cudaHostAlloc((void**)&h->h_rec, 2 * LM_REC * sizeof(double), cudaHostAllocDefault));
     for (int i = 0; i < 2; i++) CU(cudaEventCreateWithFlags(&h->ev_rec[i], cudaEventDisableTiming));
@@ -1060,11 +1062,13 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
   ST(launch_setup(h, which));
   if (h->ntiles) {
     const size_t smem = (size_t)K1_WARPS * (k1_rows_doubles(h->rowstride) + K1_EXTRA) * sizeof(double);
-    const int grid = (h->ntiles + K1_WARPS * K1_TPW - 1) / (K1_WARPS * K1_TPW);
+    // persistent warps: four CTAs per SM (registers), each warp draws tiles from d_ticket
+    const int grid = std::min((h->ntiles + K1_WARPS - 1) / K1_WARPS, 4 * std::max(h->sms, 1));
+    CU(cudaMemsetAsync(h->d_ticket, 0, sizeof(unsigned int), h->stream));
     KScope ks(h, KC_TILE_NORMAL);
 #define MCC_LAUNCH_TILE_NORMAL(RS, MMA)                                                                                                     \
     k_tile_normal<RS, MMA><<<grid, K1_WARPS * 32, smem, h->stream>>>(h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, \
-                                                                      h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p, h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p, h->st_cur)
+                                                                      h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p, h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p, h->d_ticket, h->st_cur)
     if (h->rowstride == 15) MCC_LAUNCH_TILE_NORMAL(15, false);
     else if (h->rowstride == 21) MCC_LAUNCH_TILE_NORMAL(21, false);
     else if (h->rowstride == 20) MCC_LAUNCH_TILE_NORMAL(20, true);
@@ -1474,7 +1478,7 @@ void mcc_destroy(mcc_handle* h) {
   h->world.release(); h->image.release();
   if (h->h_scal) cudaFreeHost(h->h_scal);
   drop_iteration_graphs(h);
-  if (h->d_state) { cudaFree(h->d_state); cudaFree(h->d_rec); cudaFreeHost(h->h_rec); for (int i = 0; i < 2; i++) cudaEventDestroy(h->ev_rec[i]); }
+  if (h->d_state) { cudaFree(h->d_state); cudaFree(h->d_ticket); cudaFree(h->d_rec); cudaFreeHost(h->h_rec); for (int i = 0; i < 2; i++) cudaEventDestroy(h->ev_rec[i]); }
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   for (KPending& pe : h->ev_pending) { cudaEventDestroy(pe.a); cudaEventDestroy(pe.b); }
   if (h->tm_a) { cudaEventDestroy(h->tm_a); cudaEventDestroy(h->tm_b); }
