@@ -422,8 +422,9 @@ mcc_status ensure_device(mcc_handle* h) {
   if (!h->d_state) {
     CU(cudaMalloc((void**)&h->d_state, sizeof(LmState)));
     CU(cudaMalloc((void**)&h->d_ticket, sizeof(unsigned int)));
-    CU(cudaMalloc((void**)&h->d_rec, 2 * LM_REC * sizeof(double)));
-    CU(cudaHostAlloc((void**)&h->h_rec, 2 * LM_REC * sizeof(double), cudaHostAllocDefault));
+    CU(cudaMemset(h->d_ticket, 0, sizeof(unsigned int)));   // k_tile_normal leaves it at zero after every launch
+    CU(cudaHostAlloc((void**)&h->h_rec, 2 * LM_REC * sizeof(double), cudaHostAllocMapped));   // k_decide writes the records straight to the host
+    CU(cudaHostGetDevicePointer((void**)&h->d_rec, h->h_rec, 0));
     for (int i = 0; i < 2; i++) CU(cudaEventCreateWithFlags(&h->ev_rec[i], cudaEventDisableTiming));
   }
   if (!h->attrs_set) {
@@ -1064,7 +1065,6 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
     const size_t smem = (size_t)K1_WARPS * (k1_rows_doubles(h->rowstride) + K1_EXTRA) * sizeof(double);
     // persistent warps: four CTAs per SM (registers), each warp draws tiles from d_ticket
     const int grid = std::min((h->ntiles + K1_WARPS - 1) / K1_WARPS, 4 * std::max(h->sms, 1));
-    CU(cudaMemsetAsync(h->d_ticket, 0, sizeof(unsigned int), h->stream));
     KScope ks(h, KC_TILE_NORMAL);
 #define MCC_LAUNCH_TILE_NORMAL(RS, MMA)                                                                                                     \
     k_tile_normal<RS, MMA><<<grid, K1_WARPS * 32, smem, h->stream>>>(h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, \
@@ -1132,7 +1132,7 @@ mcc_status read_scalars(mcc_handle* h) {
 mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool speculate) {
   const int cur = h->cur, cand = 1 - cur;
   const int C = h->C;
-  CU(cudaMemsetAsync(fail_ptr(h), 0, sizeof(int), h->stream));
+  if (!h->st_cur) CU(cudaMemsetAsync(fail_ptr(h), 0, sizeof(int), h->stream));   // queued iterations: k_decide clears the flags
   {
     if (h->nslots) {
       KScope ks(h, KC_SCHUR);
@@ -1291,6 +1291,7 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
       st0.radius = radius; st0.cost = cost; st0.x_norm = x_norm; st0.gmax = gmax; st0.stop = 0; st0.pad = 0;
       st0.seq[0] = h->peer_seq[0]; st0.seq[1] = h->peer_seq[1];
       CU(cudaMemcpyAsync(h->d_state, &st0, sizeof(st0), cudaMemcpyHostToDevice, h->stream));
+      CU(cudaMemsetAsync(fail_ptr(h), 0, sizeof(int), h->stream));
       int ecur = h->cur, eblk = h->blk, queued = 0, decided = 0;
       auto enqueue = [&]() -> mcc_status {
         const int slot = queued & 1;
@@ -1302,11 +1303,10 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
           ST(r);
           {
             KScope ks(h, KC_OTHER);
-            k_decide<<<1, 32, 0, h->stream>>>(h->d_state, h->d_scal.p, o.parameter_tolerance, o.function_tolerance, o.gradient_tolerance,
+            k_decide<<<1, 32, 0, h->stream>>>(h->d_state, h->d_scal.p, fail_ptr(h), o.parameter_tolerance, o.function_tolerance, o.gradient_tolerance,
                                                o.min_relative_decrease, o.max_trust_region_radius, h->d_rec + slot * LM_REC);
           }
           CU(cudaGetLastError());
-          CU(cudaMemcpyAsync(h->h_rec + slot * LM_REC, h->d_rec + slot * LM_REC, LM_REC * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
           return MCC_OK;
         };
         if (use_graphs) {
@@ -1478,7 +1478,7 @@ void mcc_destroy(mcc_handle* h) {
   h->world.release(); h->image.release();
   if (h->h_scal) cudaFreeHost(h->h_scal);
   drop_iteration_graphs(h);
-  if (h->d_state) { cudaFree(h->d_state); cudaFree(h->d_ticket); cudaFree(h->d_rec); cudaFreeHost(h->h_rec); for (int i = 0; i < 2; i++) cudaEventDestroy(h->ev_rec[i]); }
+  if (h->d_state) { cudaFree(h->d_state); cudaFree(h->d_ticket); cudaFreeHost(h->h_rec); for (int i = 0; i < 2; i++) cudaEventDestroy(h->ev_rec[i]); }
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   for (KPending& pe : h->ev_pending) { cudaEventDestroy(pe.a); cudaEventDestroy(pe.b); }
   if (h->tm_a) { cudaEventDestroy(h->tm_a); cudaEventDestroy(h->tm_b); }
