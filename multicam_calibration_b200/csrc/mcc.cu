@@ -316,6 +316,7 @@ struct mcc_handle {
   LmState* d_state = nullptr;
   unsigned int* d_ticket = nullptr;     // tile counter of k_tile_normal's persistent warps
   const LmState* st_cur = nullptr;      // what every launch passes: d_state while the pipeline runs, else nullptr
+  DecideArgs decide{};                  // st == nullptr: k_scatter_cc takes no decision
   double* d_rec = nullptr;              // [2][LM_REC] decision records
   double* h_rec = nullptr;              // pinned mirror
   cudaEvent_t ev_rec[2] = {nullptr, nullptr};
@@ -423,7 +424,7 @@ mcc_status ensure_device(mcc_handle* h) {
     CU(cudaMalloc((void**)&h->d_state, sizeof(LmState)));
     CU(cudaMalloc((void**)&h->d_ticket, sizeof(unsigned int)));
     CU(cudaMemset(h->d_ticket, 0, sizeof(unsigned int)));   // k_tile_normal leaves it at zero after every launch
-    CU(cudaHostAlloc((void**)&h->h_rec, 2 * LM_REC * sizeof(double), cudaHostAllocMapped));   // k_decide writes the records straight to the host
+    CU(cudaHostAlloc((void**)&h->h_rec, 2 * LM_REC * sizeof(double), cudaHostAllocMapped));   // decide_body writes the records straight to the host
     CU(cudaHostGetDevicePointer((void**)&h->d_rec, h->h_rec, 0));
     for (int i = 0; i < 2; i++) CU(cudaEventCreateWithFlags(&h->ev_rec[i], cudaEventDisableTiming));
   }
@@ -1111,7 +1112,7 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
   {
     KScope ks(h, KC_REDUCE);
     k_scatter_cc<<<1, 1024, 0, h->stream>>>(h->C, h->E, h->d_cc.p, cc_sum_buf(h), h->d_col_param.p, h->d_camp[which].p, h->d_Hcc2[bo].p, h->d_gc2[bo].p, h->d_scal.p + 8,
-                                             h->nranks, h->d_scal.p, fail_ptr(h), h->st_cur);
+                                             h->nranks, h->d_scal.p, fail_ptr(h), h->decide, h->st_cur);
   }
   CU(cudaGetLastError());
   return MCC_OK;
@@ -1132,7 +1133,7 @@ mcc_status read_scalars(mcc_handle* h) {
 mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool speculate) {
   const int cur = h->cur, cand = 1 - cur;
   const int C = h->C;
-  if (!h->st_cur) CU(cudaMemsetAsync(fail_ptr(h), 0, sizeof(int), h->stream));   // queued iterations: k_decide clears the flags
+  if (!h->st_cur) CU(cudaMemsetAsync(fail_ptr(h), 0, sizeof(int), h->stream));   // queued iterations: decide_body clears the flags
   {
     if (h->nslots) {
       KScope ks(h, KC_SCHUR);
@@ -1269,7 +1270,7 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
   bool speculate = true;
   int invalid_run = 0, iter = 0;
   // Pipelined section: while steps are being accepted, iteration i+1 is queued before the host has seen the decision
-  // of iteration i.  k_decide takes that decision on the device (same tests as below); if it is anything but
+  // of iteration i.  decide_body (k_scatter_cc) takes that decision on the device (same tests as below); if it is anything but
   // "accepted, go on" it sets a stop flag that turns the already queued iteration into no-ops, and the host picks
   // up from the scalars of the deciding iteration with the ordinary code below.  The device keeps the radius, so the
   // GPU never waits for the host between accepted iterations (MCC_PIPELINE=0: always the ordinary path).
@@ -1298,15 +1299,11 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
         auto body = [&]() -> mcc_status {
           const int ccur = h->cur, cblk = h->blk;
           h->cur = ecur; h->blk = eblk; h->st_cur = h->d_state;
+          h->decide = DecideArgs{h->d_state, h->d_rec + slot * LM_REC, fail_ptr(h), o.parameter_tolerance, o.function_tolerance, o.gradient_tolerance,
+                                 o.min_relative_decrease, o.max_trust_region_radius};
           mcc_status r = launch_step(h, o, radius, true);
-          h->cur = ccur; h->blk = cblk; h->st_cur = nullptr;
+          h->cur = ccur; h->blk = cblk; h->st_cur = nullptr; h->decide = DecideArgs{};
           ST(r);
-          {
-            KScope ks(h, KC_OTHER);
-            k_decide<<<1, 32, 0, h->stream>>>(h->d_state, h->d_scal.p, fail_ptr(h), o.parameter_tolerance, o.function_tolerance, o.gradient_tolerance,
-                                               o.min_relative_decrease, o.max_trust_region_radius, h->d_rec + slot * LM_REC);
-          }
-          CU(cudaGetLastError());
           return MCC_OK;
         };
         if (use_graphs) {
