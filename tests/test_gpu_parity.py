@@ -390,3 +390,19 @@ def test_wide_rigs_match_oracle(built, ncam):
     cal, orc = _pair(rig)
     _check_solve(cal, orc)
     cal.close()
+
+
+def test_dmma_contraction_matches_oracle(small_rig, c3_rig):
+    """the optional FP64 tensor-pipe contraction of K1 (mcc_set_gram_mode(h, 1), mma.sync.m8n8k4.f64): same blocks
+    (<= 1e-10 relative to each block's max) and the same solve as the oracle, like the default FMA path"""
+    cal, orc = _pair(small_rig)
+    cal.setGramMode(1)
+    g, o = cal.normalBlocks(True), orc.normal_blocks(True)
+    for key in ("Hcc", "gc", "Hff", "gf", "Hfc"):
+        assert _rel(g[key], o[key]) <= 1e-10, (key, _rel(g[key], o[key]))
+    _check_solve(cal, orc)
+    cal.close()
+    cal, orc = _pair(c3_rig)
+    cal.setGramMode(1)
+    _check_solve(cal, orc)
+    cal.close()
