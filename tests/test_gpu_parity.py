@@ -406,3 +406,27 @@ def test_dmma_contraction_matches_oracle(small_rig, c3_rig):
     cal.setGramMode(1)
     _check_solve(cal, orc)
     cal.close()
+
+
+def test_queued_iterations_match_synchronous_path(small_rig, kat_rigs, monkeypatch):
+    """solve() queues iterations ahead of their accept / reject decision (decided on the device, replayed as CUDA
+    graphs); MCC_PIPELINE=0 / MCC_GRAPHS=0 take the ordinary synchronous path.  Same arithmetic, same decisions:
+    costs, parameters and iteration tables are bit-identical, also on a fixture with rejected steps."""
+    from multicam_calibration_b200 import capi
+    for rig in (small_rig, kat_rigs["equidistant"]):
+        results = []
+        for env in ({}, {"MCC_GRAPHS": "0"}, {"MCC_PIPELINE": "0"}):
+            for k in ("MCC_GRAPHS", "MCC_PIPELINE"):
+                monkeypatch.delenv(k, raising=False)
+            for k, v in env.items():
+                monkeypatch.setenv(k, v)
+            cal = capi.calibrator_from_rig(rig, device=0)
+            s = cal.runCalibration()
+            results.append((s.final_cost, s.num_iterations, s.num_successful, s.num_unsuccessful, s.why, cal.getParams().copy(), s.trace()))
+            cal.close()
+        ref = results[-1]
+        for r in results[:-1]:
+            assert r[:5] == ref[:5]
+            assert np.array_equal(r[5], ref[5])
+            for key in ("cost", "radius", "gradient_max", "ratio"):
+                assert np.array_equal(r[6][key], ref[6][key]), key
