@@ -557,6 +557,11 @@ static void build_lane_map(CamMeta& m, int rs) {
     for (int d = 0; d < 3; d++) b[2 + d] = m.lane_u[l] >= 0 ? m.unit_o[d][m.lane_u[l]] : (int8_t)-1;
     for (int r = 0; r < 3; r++) b[5 + r] = m.red_src[r][l];
     b[8] = m.fin_src[0][l]; b[9] = m.fin_src[1][l];
+    {
+      int bi = 0, rem = l;   // l-th block of the upper triangle, row by row
+      while (bi < m.nb && rem >= m.nb - bi) { rem -= m.nb - bi; bi++; }
+      b[10] = (int8_t)bi; b[11] = (int8_t)(bi + rem);
+    }
     std::memcpy(&m.lane_info[l], b, 16);
   }
 }
