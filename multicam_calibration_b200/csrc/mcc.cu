@@ -1867,7 +1867,7 @@ mcc_status mcc_comm_unique_id(unsigned char id[MCC_UNIQUE_ID_BYTES]) {
 
 mcc_status mcc_comm_init(mcc_handle* h, int nranks, int rank, const unsigned char id[MCC_UNIQUE_ID_BYTES]) {
   if (!h || !id || nranks < 1 || rank < 0 || rank >= nranks) return fail(h, MCC_ERR_BAD_ARG, "bad communicator arguments");
-  if (nranks == 1) { h->nranks = 1; h->rank = 0; return MCC_OK; }
+  if (nranks == 1) { h->nranks = 1; h->rank = 0; drop_iteration_graphs(h); return MCC_OK; }
   if (nranks > 64) return fail(h, MCC_ERR_BAD_ARG, "at most 64 ranks (per-rank slots of the merged all-reduce)");
   if (!nccl().ok()) return fail(h, MCC_ERR_NCCL, "libnccl.so.2 not found");
   ST(ensure_device(h));
@@ -1875,6 +1875,7 @@ mcc_status mcc_comm_init(mcc_handle* h, int nranks, int rank, const unsigned cha
   std::memcpy(u.internal, id, MCC_UNIQUE_ID_BYTES);
   NC(nccl().CommInitRank(&h->comm, nranks, u, rank));
   h->nranks = nranks; h->rank = rank;
+  drop_iteration_graphs(h);   // captured for another communicator layout
   return MCC_OK;
 }
 
