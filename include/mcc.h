@@ -193,6 +193,12 @@ const char* mcc_kernel_class_name(int c);
 mcc_status mcc_get_kernel_times(mcc_handle* h, double* ms, long long* counts, int n);
 mcc_status mcc_measure_fp64_peak(int device, double* tflops);
 
+/* Test hook (host only, no device needed; no reference counterpart): the lane -> (unit, row slice) map that the tile
+ * kernel's contraction uses for a camera with n_dist distortion coefficients when rows are `rowstride` doubles apart
+ * (15 or 21).  lane_u / lane_q: 32 entries each, -1 for idle lanes; partner: 3 x 8 partner block columns of the units
+ * (-1: none).  Returns the number of row slices, or a negative mcc_status. */
+int mcc_debug_lane_map(int n_dist, int rowstride, signed char* lane_u, signed char* lane_q, signed char* partner, int* n_units);
+
 /* No counterpart in the reference.  Sum of squared reprojection residuals of n observations of ONE camera under
  * ONE rigid transform -- the arithmetic of the residual-only pass (FrameResidual with T = double) -- for callers
  * that cannot allocate device memory at the point of the call: a per-frame quality monitor inside a live image

@@ -475,6 +475,20 @@ void drop_iteration_graphs(mcc_handle* h) {
   for (cudaGraphExec_t& g : h->it_graph) { if (g) cudaGraphExecDestroy(g); g = nullptr; }
 }
 
+// contraction units of the reduced (n_k + 7)-column Gram matrix: unit u = block column u with itself and with the block
+// columns at circular distance 1 .. (nb-1)/2; for an even block count the distance nb/2 pairs are taken by the lower
+// half of the units.  Together the units cover every block pair exactly once.
+static void build_units(CamMeta& m, int n_dist) {
+  const int rnb = (4 + n_dist + 7 + 2) / 3;
+  m.nunits = rnb;
+  for (int d = 0; d < 3; d++) for (int u = 0; u < 8; u++) m.unit_o[d][u] = -1;
+  for (int u = 0; u < rnb; u++) {
+    int nd_ = 0;
+    for (int d = 1; d <= (rnb - 1) / 2; d++) m.unit_o[nd_++][u] = (int8_t)((u + d) % rnb);
+    if (rnb % 2 == 0 && u < rnb / 2) m.unit_o[nd_++][u] = (int8_t)(u + rnb / 2);
+  }
+}
+
 // Lane -> (unit, slice) map of the K1 contraction.  A 64-bit shared load is served one half-warp at a time, so the map
 // is searched (backtracking, bounded) for one where the <= 16 lanes of each half-warp hit different 8-byte banks for
 // the unit's own block column and for every partner column; slice q reads rows q, q + ksl, ... and the row stride rs
@@ -608,19 +622,7 @@ mcc_status build_structure(mcc_handle* h) {
     for (int j = 0; j < c.nparam(); j++) m.red_col[m.intr_col + j] = h->cam_col[h->intr_off[k] + j];
     if (k > 0) for (int j = 0; j < 6; j++) m.red_col[m.ext_col + j] = h->cam_col[h->ext_off[k] + j];
     m.lut_off = k * MAXC * MAXC;
-    {
-      // contraction units of the reduced (n_k + 7)-column Gram matrix: unit u = block column u with itself and with
-      // the block columns at circular distance 1 .. (nb-1)/2; for an even block count the distance nb/2 pairs are
-      // taken by the lower half of the units
-      const int rnb = (4 + c.n_dist + 7 + 2) / 3;
-      m.nunits = rnb;
-      for (int d = 0; d < 3; d++) for (int u = 0; u < 8; u++) m.unit_o[d][u] = -1;
-      for (int u = 0; u < rnb; u++) {
-        int nd_ = 0;
-        for (int d = 1; d <= (rnb - 1) / 2; d++) m.unit_o[nd_++][u] = (int8_t)((u + d) % rnb);
-        if (rnb % 2 == 0 && u < rnb / 2) m.unit_o[nd_++][u] = (int8_t)(u + rnb / 2);
-      }
-    }
+    build_units(m, c.n_dist);
     if (c.active) { max_nb = std::max(max_nb, m.nb); max_nblk = std::max(max_nblk, m.nblk); max_red_cols = std::max(max_red_cols, 4 + c.n_dist + 7); }
   }
   for (int k = 0; k < ncam; k++) {
@@ -1923,6 +1925,18 @@ mcc_status mcc_timer_stop(mcc_handle* h, double* ms) {
   CU(cudaEventElapsedTime(&f, h->tm_a, h->tm_b));
   *ms = f;
   return MCC_OK;
+}
+
+int mcc_debug_lane_map(int n_dist, int rowstride, signed char* lane_u, signed char* lane_q, signed char* partner, int* n_units) {
+  if (n_dist < 0 || n_dist > MCC_MAX_DIST || !lane_u || !lane_q || !partner || !n_units) return MCC_ERR_BAD_ARG;
+  CamMeta m;
+  std::memset(&m, 0, sizeof(m));
+  build_units(m, n_dist);
+  build_lane_map(m, rowstride);
+  for (int l = 0; l < 32; l++) { lane_u[l] = m.lane_u[l]; lane_q[l] = m.lane_q[l]; }
+  for (int d = 0; d < 3; d++) for (int u = 0; u < 8; u++) partner[d * 8 + u] = m.unit_o[d][u];
+  *n_units = m.nunits;
+  return m.ksl;
 }
 
 mcc_status mcc_measure_fp64_peak(int device, double* tflops) {
