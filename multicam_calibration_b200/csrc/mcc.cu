@@ -434,8 +434,9 @@ mcc_status ensure_device(mcc_handle* h) {
     CU((cudaFuncSetAttribute(k_tile_normal<20, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
     CU((cudaFuncSetAttribute(k_tile_normal<28, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
     CU(cudaFuncSetAttribute(k_group_setup, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SETUP_SMEM_BYTES));
-    CU(cudaFuncSetAttribute(k_schur_syrk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    CU(cudaFuncSetAttribute(k_schur_syrk<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CU((cudaFuncSetAttribute(k_schur_syrk<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)));
+    CU((cudaFuncSetAttribute(k_schur_syrk<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)));
+    CU((cudaFuncSetAttribute(k_schur_syrk<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)));
     CU(cudaFuncSetAttribute(k_solve_cam<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 196 * 1024));
     h->attrs_set = true;
   }
@@ -1148,18 +1149,22 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
                                                                     h->d_Lf.p, h->d_Linv.p, h->d_zf.p, fail_ptr(h), h->st_cur);
     }
     CU(cudaGetLastError());
-    const size_t smem0 = std::max(((size_t)SY_FB * 6 * h->LD + 2 * SY_FB * (36 + 18)) * sizeof(double), (size_t)SY_THREADS * (SY_T * SY_T + 1) * sizeof(double));
-    const size_t smem1 = smem0 + (size_t)SY_FB * 6 * C * sizeof(double);
-    const bool pf = smem1 <= 112 * 1024;   // keep two CTAs per SM; wider systems read Hfc straight from global memory
+    auto schur_smem = [&](int fb, bool pf) {
+      size_t b = ((size_t)fb * 6 * h->LD + 2 * fb * (36 + 18)) * sizeof(double);
+      if (pf) b += (size_t)fb * 6 * C * sizeof(double);
+      return std::max(b, (size_t)SY_THREADS * (SY_T * SY_T + 1) * sizeof(double));
+    };
     dim3 grid(h->sy_gx, h->sy_gy);
     {
       KScope ks(h, KC_SCHUR);
-      if (pf)
-        k_schur_syrk<true><<<grid, SY_THREADS, smem1, h->stream>>>(h->nslots, C, h->LD, h->npairs, h->d_Hfc2[h->blk].p, h->d_scale_f.p, h->d_scale_c.p, h->d_Lf.p,
-                                                                   h->d_Linv.p, h->d_zf.p, h->d_S_part.p, h->st_cur);
-      else
-        k_schur_syrk<false><<<grid, SY_THREADS, smem0, h->stream>>>(h->nslots, C, h->LD, h->npairs, h->d_Hfc2[h->blk].p, h->d_scale_f.p, h->d_scale_c.p, h->d_Lf.p,
-                                                                    h->d_Linv.p, h->d_zf.p, h->d_S_part.p, h->st_cur);
+#define MCC_LAUNCH_SCHUR(PF, FB)                                                                                                                   \
+      k_schur_syrk<PF, FB><<<grid, SY_THREADS, schur_smem(FB, PF), h->stream>>>(h->nslots, C, h->LD, h->npairs, h->d_Hfc2[h->blk].p, h->d_scale_f.p,     \
+                                                                                h->d_scale_c.p, h->d_Lf.p, h->d_Linv.p, h->d_zf.p, h->d_S_part.p, h->st_cur)
+      // prefetch variants keep two CTAs per SM (<= 112 KB each): 8 frames per batch, else 4; wider systems read Hfc from global memory
+      if (schur_smem(8, true) <= 112 * 1024) MCC_LAUNCH_SCHUR(true, 8);
+      else if (schur_smem(4, true) <= 112 * 1024) MCC_LAUNCH_SCHUR(true, 4);
+      else MCC_LAUNCH_SCHUR(false, 8);
+#undef MCC_LAUNCH_SCHUR
     }
     CU(cudaGetLastError());
     const int n = h->npairs * SY_T * SY_T;
