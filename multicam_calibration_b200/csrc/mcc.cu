@@ -722,7 +722,7 @@ mcc_status build_structure(mcc_handle* h) {
       int done = 0;
       for (int t = 0; t < nt; t++) {
         const int cnt = std::min(n - done, (base + (t < rem ? 1 : 0)) * 32);
-        tiles.push_back(Tile{(int)(o0 + done), cnt, s * ncam + k});
+        tiles.push_back(Tile{(int)(o0 + done), cnt, s * ncam + k, k});
         done += cnt;
       }
     }
