@@ -171,13 +171,12 @@ mcc_status mcc_eval_normal_blocks(mcc_handle* h, int use_loss, double* cost, dou
  * single-process (calibrator.cpp:303 only sets Ceres' thread count). */
 mcc_status mcc_comm_unique_id(unsigned char id[MCC_UNIQUE_ID_BYTES]);
 mcc_status mcc_comm_init(mcc_handle* h, int nranks, int rank, const unsigned char id[MCC_UNIQUE_ID_BYTES]);
-
-/* How the per-tile Gram matrix [J r]^T [J r] is contracted (no reference counterpart: Ceres forms J^T J on the CPU).
- * 0 (default): FP64 FMA pipe, 3x3 register blocks per lane.  1: FP64 tensor pipe, mma.sync.m8n8k4 (DMMA).
- * Both are IEEE fp64 with fused multiply-adds; only the summation order differs.  The environment variable
- * MCC_GRAM=dmma|fma sets the initial mode of new handles. */
-mcc_status mcc_set_gram_mode(mcc_handle* h, int mode);
-int mcc_get_gram_mode(const mcc_handle* h);
+/* How the per-iteration sums travel between the ranks of this handle: 0 = single rank, 1 = the library's own one-shot
+ * all-reduce over NVLink peer windows, 2 = NCCL.  Valid after the first mcc_upload / mcc_run.  An exchange over peer windows
+ * waits at most MCC_PEER_TIMEOUT_S seconds (environment, default 60) for another rank; after that the call fails with
+ * MCC_ERR_NCCL "peer exchange timed out" (NCCL would wait forever).  A rank whose frame shard is empty still has to make
+ * the same mcc_* calls as the others. */
+int mcc_comm_transport(const mcc_handle* h);
 
 /* Measurement hooks for bench.py (no reference counterpart: Ceres only prints wall-clock phase times,
  * calibrator.cpp:312).  mcc_timer_start/stop bracket a region with CUDA events on the handle's stream (the
@@ -215,7 +214,12 @@ int mcc_debug_lane_map(int n_dist, int rowstride, signed char* lane_u, signed ch
  * MCC_NOALLOC_MAX_OBS / 128 doubles (256 KiB, held by every GPU that loads the library until the process exits).
  * n > MCC_NOALLOC_MAX_OBS is rejected with MCC_ERR_TOO_LARGE (message in errbuf, which may be NULL).
  * The FIRST call on each device looks up the array's device address (cudaGetSymbolAddress, that device current);
- * make that first call outside any stream capture.  All calls on a device share the one array, which keeps the
+ * make that first call outside any stream capture.  Under CUDA's lazy module loading that first call (like the first
+ * launch of any kernel of this library) also makes the driver load the library's device code and the 256 KiB array,
+ * which takes device memory and may synchronise the context: make one warm-up call per device at start-up, before the
+ * remaining memory is handed to another allocator and before the latency-critical section begins.  The looked-up address
+ * is cached per device ordinal for the life of the process and is not valid across cudaDeviceReset.
+ * All calls on a device share the one array, which keeps the
  * previous call's partial sums: every slot a call reads it has first overwritten itself, so nothing needs
  * clearing, but two calls whose kernels overlap on the GPU (different streams, or several host threads) race on
  * it -- serialise them on one stream. */

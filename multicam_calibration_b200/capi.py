@@ -69,10 +69,10 @@ SYMBOLS = ["mcc_version", "mcc_default_options", "mcc_summary_size", "mcc_create
            "mcc_set_cameras", "mcc_set_fix_all_intrinsics", "mcc_set_camera_flags", "mcc_add_frame", "mcc_add_frames", "mcc_clear_frames",
            "mcc_num_frames", "mcc_num_observations", "mcc_init_params", "mcc_num_params", "mcc_get_params", "mcc_set_params", "mcc_upload",
            "mcc_run", "mcc_get_camera", "mcc_num_residuals", "mcc_eval_residuals", "mcc_eval_cost", "mcc_remove_outliers", "mcc_get_mask",
-           "mcc_set_mask", "mcc_num_reduced_cam_cols", "mcc_num_active_frames", "mcc_eval_normal_blocks", "mcc_comm_unique_id", "mcc_comm_init",
+           "mcc_set_mask", "mcc_num_reduced_cam_cols", "mcc_num_active_frames", "mcc_eval_normal_blocks", "mcc_comm_unique_id", "mcc_comm_init", "mcc_comm_transport",
            "mcc_transform_to_rvec_tvec", "mcc_rvec_tvec_to_transform", "mcc_timer_start", "mcc_timer_stop", "mcc_set_kernel_timing",
            "mcc_num_kernel_classes", "mcc_kernel_class_name", "mcc_get_kernel_times", "mcc_measure_fp64_peak", "mcc_debug_lane_map",
-           "mcc_reprojection_cost_noalloc", "mcc_set_gram_mode", "mcc_get_gram_mode", "mcc_init_pose"]
+           "mcc_reprojection_cost_noalloc", "mcc_init_pose"]
 
 
 def build(force: bool = False) -> str:
@@ -129,6 +129,7 @@ def lib():
     L.mcc_eval_normal_blocks.argtypes = [vp, C.c_int, dp, dp, dp, dp, dp, dp, ip]
     L.mcc_comm_unique_id.argtypes = [C.POINTER(C.c_ubyte)]
     L.mcc_comm_init.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_ubyte)]
+    L.mcc_comm_transport.argtypes = [vp]
     L.mcc_transform_to_rvec_tvec.argtypes = [dp, dp]
     L.mcc_transform_to_rvec_tvec.restype = None
     L.mcc_rvec_tvec_to_transform.argtypes = [dp, dp]
@@ -141,8 +142,6 @@ def lib():
     L.mcc_get_kernel_times.argtypes = [vp, dp, C.POINTER(C.c_longlong), C.c_int]
     L.mcc_measure_fp64_peak.argtypes = [C.c_int, dp]
     L.mcc_init_pose.argtypes = [C.c_int, dp, C.c_int, dp, C.c_int, dp, dp, dp]
-    L.mcc_set_gram_mode.argtypes = [vp, C.c_int]
-    L.mcc_get_gram_mode.argtypes = [vp]
     L.mcc_reprojection_cost_noalloc.argtypes = [C.c_int, C.c_int] + [vp, vp, C.c_size_t] + [vp] * 8 + [C.c_char_p, C.c_size_t]
     assert L.mcc_summary_size() == C.sizeof(Summary), (L.mcc_summary_size(), C.sizeof(Summary))
     _lib = L
@@ -377,10 +376,6 @@ class Calibrator:
         self._check(self._L.mcc_eval_normal_blocks(self.h, int(use_loss), C.byref(cost), _dp(Hcc) if Cc else None, _dp(gc), _dp(Hff), _dp(gf), _dp(Hfc), _ip(ids)))
         return dict(cost=cost.value, Hcc=Hcc, gc=gc[:Cc], Hff=Hff[:ns], gf=gf[:ns], Hfc=Hfc.reshape(-1)[:ns * 6 * Cc].reshape(ns, 6, Cc), frames=ids[:ns])
 
-    def setGramMode(self, mode: int):
-        """0: FP64 FMA register blocks (default); 1: FP64 mma.sync (DMMA) tiles"""
-        self._check(self._L.mcc_set_gram_mode(self.h, int(mode)))
-
     def timerStart(self):
         self._check(self._L.mcc_timer_start(self.h))
 
@@ -403,6 +398,10 @@ class Calibrator:
     def commInit(self, nranks: int, rank: int, unique_id: bytes):
         buf = (C.c_ubyte * UNIQUE_ID_BYTES).from_buffer_copy(unique_id)
         self._check(self._L.mcc_comm_init(self.h, nranks, rank, buf))
+
+    def commTransport(self) -> int:
+        """0: single rank, 1: peer windows, 2: NCCL (valid after the first upload / run)"""
+        return int(self._L.mcc_comm_transport(self.h))
 
 
 def calibrator_from_rig(rig: Rig, device: Optional[int] = None) -> Calibrator:

@@ -232,7 +232,7 @@ void parallel_memcpy(void* dst, const void* src, size_t bytes) {
 }
 
 // kernel categories for the optional per-launch CUDA-event timing (mcc_set_kernel_timing)
-enum { KC_SETUP = 0, KC_TILE_NORMAL, KC_ASSEMBLE, KC_SCHUR, KC_SOLVE, KC_BACKSUB, KC_TILE_COST, KC_REDUCE, KC_OTHER, KC_COUNT };
+enum { KC_SETUP = 0, KC_TILE_NORMAL, KC_ASSEMBLE, KC_SCHUR, KC_SOLVE, KC_BACKSUB, KC_TILE_COST, KC_REDUCE, KC_OTHER, KC_EXCHANGE, KC_COUNT };
 struct KPending { cudaEvent_t a, b; int cat; };
 
 // FP64 FMA throughput probe: 8 independent dependent-chains per thread
@@ -288,7 +288,7 @@ struct mcc_handle {
   DBuf<double> d_aos_w, d_aos_i, d_X, d_Y, d_Z, d_U, d_V, d_res;
   DBuf<uint8_t> d_mask;
   DBuf<Tile> d_tiles;
-  DBuf<int> d_gto, d_lut, d_col_param, d_hff_tab, d_cam_tiles, d_cam_chunk0;
+  DBuf<int> d_gto, d_lut, d_col_param, d_hff_tab, d_cam_tiles, d_cam_chunk0, d_tab;
   DBuf<int2> d_hfc_tab;
   DBuf<CcChunk> d_cc_chunks;
   DBuf<double> d_w_f, d_Linv, d_zf;
@@ -312,6 +312,7 @@ struct mcc_handle {
   size_t peer_nS = 0, peer_nC = 0;      // slot sizes the window was laid out for
   unsigned long long peer_seq[2] = {0, 0};
   bool peer_on = false, peer_failed = false;
+  long long peer_timeout_cycles = 0;    // k_peer_allreduce gives up after this many SM clocks (MCC_PEER_TIMEOUT_S, default 60 s)
   // iterations queued ahead of their accept / reject decision (solve(): pipelined section)
   LmState* d_state = nullptr;
   unsigned int* d_ticket = nullptr;     // tile counter of k_tile_normal's persistent warps
@@ -328,7 +329,6 @@ struct mcc_handle {
   double* h_scal = nullptr;            // pinned mirror of d_scal
   int asm_grid = 0, sy_gx = 0, sy_gy = 0;
   int sms = 0;
-  int gram_mode = 0;                   // 0: FP64 FMA 3x3 register blocks, 1: FP64 mma.sync (DMMA) 8x8 tiles
   bool attrs_set = false;
   long long launches = 0, h2d = 0, d2h = 0;
   // optional per-launch timing
@@ -429,10 +429,8 @@ mcc_status ensure_device(mcc_handle* h) {
     for (int i = 0; i < 2; i++) CU(cudaEventCreateWithFlags(&h->ev_rec[i], cudaEventDisableTiming));
   }
   if (!h->attrs_set) {
-    CU((cudaFuncSetAttribute(k_tile_normal<15, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
-    CU((cudaFuncSetAttribute(k_tile_normal<21, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
-    CU((cudaFuncSetAttribute(k_tile_normal<20, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
-    CU((cudaFuncSetAttribute(k_tile_normal<28, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
+    CU((cudaFuncSetAttribute(k_tile_normal<15>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
+    CU((cudaFuncSetAttribute(k_tile_normal<21>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
     CU(cudaFuncSetAttribute(k_group_setup, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SETUP_SMEM_BYTES));
     CU((cudaFuncSetAttribute(k_schur_syrk<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)));
     CU((cudaFuncSetAttribute(k_schur_syrk<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)));
@@ -494,7 +492,7 @@ static void build_units(CamMeta& m, int n_dist) {
 // is searched (backtracking, bounded) for one where the <= 16 lanes of each half-warp hit different 8-byte banks for
 // the unit's own block column and for every partner column; slice q reads rows q, q + ksl, ... and the row stride rs
 // is odd.  Slice counts of the form 2^n or 3 * 2^n only (the reduction handles those).  Falls back to
-// lane = q * nunits + u when no conflict-free map exists (or for the even strides of the MMA path, which ignores it).
+// lane = q * nunits + u when no conflict-free map exists.
 struct LaneSearch {
   int n;
   int bank[64][4];
@@ -638,9 +636,8 @@ mcc_status build_structure(mcc_handle* h) {
       }
   }
   h->gstride = 9 * max_nblk;
-  // k_tile_normal<RS, MMA> works on reduced rows of (4 + n_dist) + 7 columns
-  if (h->gram_mode == 0) h->rowstride = (max_red_cols + 2) / 3 <= 5 ? 15 : 21;
-  else h->rowstride = (max_red_cols + 7) / 8 <= 2 ? 20 : 28;
+  // k_tile_normal<RS> works on reduced rows of (4 + n_dist) + 7 columns
+  h->rowstride = (max_red_cols + 2) / 3 <= 5 ? 15 : 21;
   for (int k = 0; k < ncam; k++) build_lane_map(cm[k], h->rowstride);
 
   // reduced column -> (camera, local column)
@@ -865,7 +862,8 @@ mcc_status ensure_comm_windows(mcc_handle* h);
 mcc_status ensure_peer_window(mcc_handle* h);
 
 mcc_status prepare(mcc_handle* h) {
-  if (h->cams.empty() || h->nframes == 0) return fail(h, MCC_ERR_NO_DATA, "no data to run on!");
+  // several ranks: a rank whose shard is empty still takes part in every collective (with empty launches)
+  if (h->cams.empty() || (h->nframes == 0 && h->nranks <= 1)) return fail(h, MCC_ERR_NO_DATA, "no data to run on!");
   ST(ensure_device(h));
   for (const CamHost& c : h->cams)
     if (c.active && c.model != MCC_MODEL_EQUIDISTANT && c.model != MCC_MODEL_RADTAN) return fail(h, MCC_ERR_BAD_MODEL, "unknown distortion model: %d", c.model);
@@ -956,11 +954,10 @@ mcc_status ensure_comm_windows(mcc_handle* h) {
 
 void free_peer_window(mcc_handle* h) {
   if (!h->peer_own) return;
+  // No collective here (a handle may be destroyed on one rank only, e.g. on an error path).  It is safe after any completed
+  // solve or evaluation: an exchange returns on this rank only once EVERY rank's cells of that exchange have arrived, and
+  // a peer stores into this window again only in a later exchange, i.e. in a later call that this rank takes part in.
   cudaStreamSynchronize(h->stream);
-  if (h->comm) {   // nobody may still be storing into a window that is about to go away
-    nccl().AllReduce(fail_ptr(h), fail_ptr(h), 1, ncclInt32_, ncclMax_, h->comm, h->stream);
-    cudaStreamSynchronize(h->stream);
-  }
   for (int r = 0; r < h->pw.nranks; r++)
     if (r != h->pw.rank && h->pw.base[r]) cudaIpcCloseMemHandle(h->pw.base[r]);
   cudaFree(h->peer_own);
@@ -986,52 +983,67 @@ mcc_status ensure_peer_window(mcc_handle* h) {
   cudaIpcMemHandle_t mine;
   std::memset(&mine, 0, sizeof(mine));
   if (!bad) {
-    CU(cudaMemsetAsync(h->peer_own, 0, cells * sizeof(uint4), h->stream));
+    if (cudaMemsetAsync(h->peer_own, 0, cells * sizeof(uint4), h->stream) != cudaSuccess) bad = 1;
     if (cudaIpcGetMemHandle(&mine, h->peer_own) != cudaSuccess) bad = 1;
   }
   cudaGetLastError();
-  // gather the handles: every rank fills its own 64 bytes of a zeroed table, the int32 sum is the concatenation
+  // gather the handles: every rank fills its own 64 bytes of a zeroed table, the int32 sum is the concatenation.
+  // This is a handshake: a rank that fails locally must still take part in both all-reduces (with bad = 1), or the
+  // others would wait for it forever; only a failing NCCL call itself ends it early.
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
   const size_t tab_ints = (size_t)R * 16 + 1;   // + the failure count
   std::vector<int> tab(tab_ints, 0);
   std::memcpy(&tab[(size_t)h->rank * 16], &mine, 64);
-  tab[(size_t)R * 16] = bad;
-  int* d_tab = nullptr;
-  CU(cudaMalloc((void**)&d_tab, tab_ints * sizeof(int)));
-  CU(cudaMemcpyAsync(d_tab, tab.data(), tab_ints * sizeof(int), cudaMemcpyHostToDevice, h->stream));
-  NC(nccl().AllReduce(d_tab, d_tab, tab_ints, ncclInt32_, ncclSum_, h->comm, h->stream));
-  CU(cudaMemcpyAsync(tab.data(), d_tab, tab_ints * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-  CU(cudaStreamSynchronize(h->stream));
-  bad = tab[(size_t)R * 16];
+  CU(h->d_tab.reserve(tab_ints));                // grow-only member buffer: freed with the handle, never leaked
+  int* d_tab = h->d_tab.p;
   PeerWin pw{};
   pw.nranks = R; pw.rank = h->rank;
-  if (!bad) {
-    for (int r = 0; r < R; r++) {
-      if (r == h->rank) { pw.base[r] = h->peer_own; continue; }
-      cudaIpcMemHandle_t hd;
-      std::memcpy(&hd, &tab[(size_t)r * 16], 64);
-      void* p = nullptr;
-      if (cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { bad = 1; cudaGetLastError(); break; }
-      pw.base[r] = (uint4*)p;
+  int one = 1;
+  mcc_status hs = MCC_OK;
+  auto agree = [&](size_t n) -> bool {           // sum over the ranks of tab[0..n); false = the transport itself failed
+    bool local_ok = cudaMemcpyAsync(d_tab, tab.data(), n * sizeof(int), cudaMemcpyHostToDevice, h->stream) == cudaSuccess;
+    if (nccl().AllReduce(d_tab, d_tab, n, ncclInt32_, ncclSum_, h->comm, h->stream) != 0) return false;
+    local_ok = local_ok && cudaMemcpyAsync(tab.data(), d_tab, n * sizeof(int), cudaMemcpyDeviceToHost, h->stream) == cudaSuccess;
+    local_ok = cudaStreamSynchronize(h->stream) == cudaSuccess && local_ok;
+    if (!local_ok) { cudaGetLastError(); tab[n - 1] = 1; }   // count as a failure of this rank; the next agreement spreads it
+    return true;
+  };
+  tab[(size_t)R * 16] = bad;
+  if (!agree(tab_ints)) hs = fail(h, MCC_ERR_NCCL, "peer-window handshake: ncclAllReduce failed");
+  if (hs == MCC_OK) {
+    bad = tab[(size_t)R * 16];
+    if (!bad) {
+      for (int r = 0; r < R; r++) {
+        if (r == h->rank) { pw.base[r] = h->peer_own; continue; }
+        cudaIpcMemHandle_t hd;
+        std::memcpy(&hd, &tab[(size_t)r * 16], 64);
+        void* p = nullptr;
+        if (cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { bad = 1; cudaGetLastError(); break; }
+        pw.base[r] = (uint4*)p;
+      }
     }
+    // second agreement: did everybody manage to map everybody?
+    tab[0] = bad;
+    if (!agree(1)) hs = fail(h, MCC_ERR_NCCL, "peer-window handshake: ncclAllReduce failed");
+    else one = tab[0];
   }
-  // second agreement: did everybody manage to map everybody?
-  int one = bad;
-  CU(cudaMemcpyAsync(d_tab, &one, sizeof(int), cudaMemcpyHostToDevice, h->stream));
-  NC(nccl().AllReduce(d_tab, d_tab, 1, ncclInt32_, ncclSum_, h->comm, h->stream));
-  CU(cudaMemcpyAsync(&one, d_tab, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-  CU(cudaStreamSynchronize(h->stream));
-  cudaFree(d_tab);
   h->pw = pw;
   if (std::getenv("MCC_COMM_DEBUG")) std::fprintf(stderr, "[mcc rank %d] peer window %zu B: %s\n", h->rank, cells * sizeof(uint4), one == 0 ? "mapped on all ranks" : "not available, NCCL");
-  if (one != 0) {
+  if (one != 0 || hs != MCC_OK) {
     for (int r = 0; r < R; r++)
       if (r != h->rank && pw.base[r]) cudaIpcCloseMemHandle(pw.base[r]);
     if (h->peer_own) cudaFree(h->peer_own);
+    cudaGetLastError();
     h->peer_own = nullptr; h->pw = PeerWin{}; h->peer_on = false;
     // remember the sizes so that the attempt is not repeated on every run
     h->peer_nS = nS; h->peer_nC = nC; h->peer_failed = true;
-    return MCC_OK;
+    return hs;
+  }
+  {
+    // how long an exchange waits for a peer before it gives up (SM clocks; clock64 runs at the SM clock, <= ~2 GHz)
+    double secs = 60.0;
+    if (const char* e = std::getenv("MCC_PEER_TIMEOUT_S")) { const double v = std::atof(e); if (v > 0.0) secs = v; }
+    h->peer_timeout_cycles = (long long)(secs * 2.0e9);
   }
   h->peer_nS = nS; h->peer_nC = nC; h->peer_seq[0] = h->peer_seq[1] = 0; h->peer_on = true;
   return MCC_OK;
@@ -1048,13 +1060,17 @@ mcc_status peer_allreduce(mcc_handle* h, int ex, double* p, size_t n) {
   const size_t off = base + (seq & 1) * (size_t)R * slot_n;
   // the sequence number in the cells is 32 bits and never 0 (0 = a fresh window)
   const unsigned int seq32 = (unsigned int)(seq % 0xffffffffull) + 1u;
-  k_peer_allreduce<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->pw, p, (int)n, off, seq32, ex, base, slot_n, fail_ptr(h), h->st_cur);
+  {
+    KScope ks(h, KC_EXCHANGE);   // includes the wait for the slowest rank
+    k_peer_allreduce<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->pw, p, (int)n, off, seq32, ex, base, slot_n, fail_ptr(h), h->peer_timeout_cycles, h->st_cur);
+  }
   CU(cudaGetLastError());
   return MCC_OK;
 }
 
 mcc_status allreduce(mcc_handle* h, double* p, size_t n, int op) {
   if (h->nranks <= 1 || n == 0) return MCC_OK;
+  KScope ks(h, KC_EXCHANGE);
   NC(nccl().AllReduce(p, p, n, ncclFloat64_, op, h->comm, h->stream));
   return MCC_OK;
 }
@@ -1075,13 +1091,11 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
     // persistent warps: four CTAs per SM (registers), each warp draws tiles from d_ticket
     const int grid = std::min((h->ntiles + K1_WARPS - 1) / K1_WARPS, 4 * std::max(h->sms, 1));
     KScope ks(h, KC_TILE_NORMAL);
-#define MCC_LAUNCH_TILE_NORMAL(RS, MMA)                                                                                                     \
-    k_tile_normal<RS, MMA><<<grid, K1_WARPS * 32, smem, h->stream>>>(h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, \
+#define MCC_LAUNCH_TILE_NORMAL(RS)                                                                                                          \
+    k_tile_normal<RS><<<grid, K1_WARPS * 32, smem, h->stream>>>(h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, \
                                                                       h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p, h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p, h->d_ticket, h->st_cur)
-    if (h->rowstride == 15) MCC_LAUNCH_TILE_NORMAL(15, false);
-    else if (h->rowstride == 21) MCC_LAUNCH_TILE_NORMAL(21, false);
-    else if (h->rowstride == 20) MCC_LAUNCH_TILE_NORMAL(20, true);
-    else MCC_LAUNCH_TILE_NORMAL(28, true);
+    if (h->rowstride == 15) MCC_LAUNCH_TILE_NORMAL(15);
+    else MCC_LAUNCH_TILE_NORMAL(21);
 #undef MCC_LAUNCH_TILE_NORMAL
     CU(cudaGetLastError());
   }
@@ -1126,12 +1140,24 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
   return MCC_OK;
 }
 
+// failure flags of an iteration (d_scal[32]): 1 pose block not positive definite, 2 reduced system not positive definite,
+// 4 non-finite step -- all three mean "invalid step" to the trust-region loop -- and 16: a peer exchange gave up waiting
+// for another rank, which is not a property of the step but a broken job: reported as an error, peer windows are dropped.
+mcc_status check_flags(mcc_handle* h, int flags) {
+  if (flags & 16) {
+    h->peer_on = false; h->peer_failed = true;
+    return fail(h, MCC_ERR_NCCL, "peer exchange timed out: rank %d waited more than %.0f s for another rank's part of an all-reduce (did every rank enter "
+                "the same mcc_* call? MCC_PEER_TIMEOUT_S raises the limit, MCC_P2P=0 uses NCCL, which waits forever)", h->rank, (double)h->peer_timeout_cycles / 2.0e9);
+  }
+  return MCC_OK;
+}
+
 mcc_status read_scalars(mcc_handle* h) {
   CU(cudaMemcpyAsync(h->h_scal, h->d_scal.p, 33 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));   // scalars + failure flags
   CU(cudaStreamSynchronize(h->stream));
   h->d2h += 33 * sizeof(double);
   if (h->ktiming) resolve_ktiming(h);
-  return MCC_OK;
+  return check_flags(h, *reinterpret_cast<const int*>(h->h_scal + 32));
 }
 
 // K2..K5 for one trust-region radius: candidate parameters in the other buffer, scalars in d_scal[3..6], [10..12]
@@ -1358,6 +1384,7 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
           // the iteration that stopped the pipeline: hand its scalars to the ordinary code (what is queued behind it does nothing)
           CU(cudaStreamSynchronize(h->stream));
           std::memcpy(h->h_scal, rec, 33 * sizeof(double));
+          ST(check_flags(h, *reinterpret_cast<const int*>(h->h_scal + 32)));
           have_scalars = true;
           break;
         }
@@ -1466,7 +1493,6 @@ mcc_status mcc_create(mcc_handle** out) {
   if (!out) return MCC_ERR_BAD_ARG;
   *out = new (std::nothrow) mcc_handle();
   if (!*out) return MCC_ERR_BAD_ARG;
-  if (const char* e = std::getenv("MCC_GRAM")) (*out)->gram_mode = (std::strcmp(e, "dmma") == 0) ? 1 : 0;
   return MCC_OK;
 }
 
@@ -1481,7 +1507,7 @@ void mcc_destroy(mcc_handle* h) {
                         &h->d_mcc_f, &h->d_dx2_f, &h->d_xn2c_f, &h->d_cc_part, &h->d_cc_sum, &h->d_Hcc2[0], &h->d_Hcc2[1], &h->d_gc2[0], &h->d_gc2[1], &h->d_scale_c, &h->d_scale_f, &h->d_S_part,
                         &h->d_S_sum, &h->d_M, &h->d_yc, &h->d_ysc, &h->d_scal};
   for (auto* b : dd) b->release();
-  h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_lut.release(); h->d_col_param.release(); 
+  h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_tab.release(); h->d_lut.release(); h->d_col_param.release(); 
   h->d_cams.release(); h->d_cc.release(); h->d_colmap.release(); h->d_hff_tab.release(); h->d_hfc_tab.release();
   h->d_cam_tiles.release(); h->d_cam_chunk0.release(); h->d_cc_chunks.release(); h->d_w_f.release(); h->d_Linv.release(); h->d_zf.release();
   h->world.release(); h->image.release();
@@ -1684,7 +1710,7 @@ mcc_status mcc_run(mcc_handle* h, const mcc_options* opts, mcc_summary* out) {
   mcc_summary local;
   mcc_summary& S = out ? *out : local;
   std::memset(&S, 0, sizeof(S));
-  if (h->cams.empty() || h->nframes == 0) {
+  if (h->cams.empty() || (h->nframes == 0 && h->nranks <= 1)) {
     std::fprintf(stderr, "no data to run on!\n");   // calibrator.cpp:287
     S.termination = 2; S.why = 7;
     return fail(h, MCC_ERR_NO_DATA, "no data to run on!");
@@ -1886,12 +1912,10 @@ mcc_status mcc_comm_init(mcc_handle* h, int nranks, int rank, const unsigned cha
   return MCC_OK;
 }
 
-mcc_status mcc_set_gram_mode(mcc_handle* h, int mode) {
-  if (!h || (mode != 0 && mode != 1)) return MCC_ERR_BAD_ARG;
-  if (h->gram_mode != mode) { h->gram_mode = mode; h->structure_dirty = true; }
-  return MCC_OK;
+int mcc_comm_transport(const mcc_handle* h) {
+  if (!h || h->nranks <= 1) return 0;
+  return h->peer_on ? 1 : 2;
 }
-int mcc_get_gram_mode(const mcc_handle* h) { return h ? h->gram_mode : -1; }
 
 mcc_status mcc_set_kernel_timing(mcc_handle* h, int enabled) {
   if (!h) return MCC_ERR_BAD_ARG;
@@ -1902,7 +1926,7 @@ mcc_status mcc_set_kernel_timing(mcc_handle* h, int enabled) {
 
 int mcc_num_kernel_classes(void) { return KC_COUNT; }
 const char* mcc_kernel_class_name(int c) {
-  static const char* names[KC_COUNT] = {"group_setup", "tile_normal", "frame_assemble", "schur_syrk", "solve_cam", "backsub", "tile_cost", "reduce", "other"};
+  static const char* names[KC_COUNT] = {"group_setup", "tile_normal", "frame_assemble", "schur_syrk", "solve_cam", "backsub", "tile_cost", "reduce", "other", "exchange"};
   return (c >= 0 && c < KC_COUNT) ? names[c] : "";
 }
 

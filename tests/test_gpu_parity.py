@@ -392,18 +392,19 @@ def test_wide_rigs_match_oracle(built, ncam):
     cal.close()
 
 
-def test_dmma_contraction_matches_oracle(small_rig, c3_rig):
-    """the optional FP64 tensor-pipe contraction of K1 (mcc_set_gram_mode(h, 1), mma.sync.m8n8k4.f64): same blocks
-    (<= 1e-10 relative to each block's max) and the same solve as the oracle, like the default FMA path"""
-    cal, orc = _pair(small_rig)
-    cal.setGramMode(1)
+@pytest.mark.parametrize("config,nframes", [("c4", 200), ("c5", 64)])
+def test_bench_configs_match_oracle(built, config, nframes):
+    """the two configurations every performance number is quoted on (BASELINE.json configs[3], configs[4]), at a frame
+    count the oracle solves in seconds: same generator, same seed, same cameras as bench.py's workload.  Blocks
+    <= 1e-10 relative, solve at the north-star tolerances with the same iteration count."""
+    from multicam_calibration_b200 import synth
+    rig = (synth.config_c4 if config == "c4" else synth.config_c5)(nframes=nframes)
+    assert rig.num_cameras == (8 if config == "c4" else 16)
+    cal, orc = _pair(rig)
     g, o = cal.normalBlocks(True), orc.normal_blocks(True)
+    assert abs(g["cost"] - o["cost"]) <= 1e-12 * o["cost"]
     for key in ("Hcc", "gc", "Hff", "gf", "Hfc"):
         assert _rel(g[key], o[key]) <= 1e-10, (key, _rel(g[key], o[key]))
-    _check_solve(cal, orc)
-    cal.close()
-    cal, orc = _pair(c3_rig)
-    cal.setGramMode(1)
     _check_solve(cal, orc)
     cal.close()
 

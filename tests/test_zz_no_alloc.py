@@ -1,4 +1,4 @@
-"""GPU: mcc_reprojection_cost_noalloc against the handle-based mcc_eval_cost.
+"""GPU: mcc_reprojection_cost_noalloc against the handle-based mcc_eval_cost and against the CPU oracle.
 
 The no-alloc entry point exists for callers that cannot allocate device memory when they need a cost (a live
 per-frame monitor that must not hit cudaMalloc's device-wide sync; a process whose GPU memory belongs to another
@@ -45,7 +45,16 @@ def _existing(rig, mask):
     return c
 
 
-def _noalloc(rig, mask):
+def _oracle(rig, mask):
+    """the CPU oracle's cost without loss, 1/2 sum r^2 (oracle.cpp: FrameResidual with T = double)"""
+    import oracle
+    o = oracle.Oracle(rig)
+    if mask is not None:
+        o.set_mask(mask)
+    return o.cost(use_loss=False)
+
+
+def _noalloc(rig, mask, check_no_alloc=False):
     import torch
     from multicam_calibration_b200 import capi
     cam = rig.cameras[0]
@@ -59,9 +68,14 @@ def _noalloc(rig, mask):
     m = torch.tensor(mask, dtype=torch.uint8, device=dev) if mask is not None else None
     out = torch.full((1,), -1.0, dtype=torch.float64, device=dev)
     torch.cuda.synchronize()
+    free_before = torch.cuda.mem_get_info(0)[0]
     capi.reprojection_cost_noalloc(cam.model_id, len(cam.distortion_coeffs), intr.data_ptr(), Rt.data_ptr(), rig.num_obs,
                                    *[c.data_ptr() for c in cols], m.data_ptr() if m is not None else None, out.data_ptr(), 0)
     torch.cuda.synchronize()
+    if check_no_alloc:
+        # the device's free memory is what it was: the call took nothing (only meaningful once the module is loaded,
+        # i.e. not for the very first call of the process, see include/mcc.h)
+        assert torch.cuda.mem_get_info(0)[0] == free_before
     return 0.5 * out.item()
 
 
@@ -73,9 +87,13 @@ def test_noalloc_matches_eval_cost_twice_in_a_row(built, model):
     mask_small = (rng.random(small.num_obs) > 0.2).astype(np.uint8)
     want_big, want_small = _existing(big, None), _existing(small, mask_small)
     got_big = _noalloc(big, None)             # first call: 1563 partial sums land in the shared scratch
-    got_small = _noalloc(small, mask_small)   # second call: 24 partial sums; the other 1539 slots are stale
+    got_small = _noalloc(small, mask_small, check_no_alloc=True)   # second call: 24 partial sums; the other 1539 slots are stale
     assert abs(got_big - want_big) <= REL_TOL * want_big, (got_big, want_big)
     assert abs(got_small - want_small) <= REL_TOL * want_small, (got_small, want_small)
+    # ... and directly against the CPU oracle, not only against another CUDA path of this library
+    for got, rig, mask in ((got_big, big, None), (got_small, small, mask_small)):
+        want = _oracle(rig, mask)
+        assert abs(got - want) <= REL_TOL * want, (got, want)
     assert want_small < 0.1 * want_big        # the two calls really differ, so a stale sum would show
 
 
