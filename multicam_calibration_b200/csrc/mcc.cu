@@ -288,19 +288,18 @@ struct mcc_handle {
   DBuf<double> d_aos_w, d_aos_i, d_X, d_Y, d_Z, d_U, d_V, d_res;
   DBuf<uint8_t> d_mask;
   DBuf<Tile> d_tiles;
-  DBuf<int> d_gto, d_lut, d_col_param, d_hff_tab, d_cam_tiles, d_cam_chunk0, d_tab;
-  DBuf<int2> d_hfc_tab;
-  DBuf<CcChunk> d_cc_chunks;
-  DBuf<double> d_w_f, d_Linv, d_zf;
-  int ncc_chunks = 0, cc_maxne = 1;
+  DBuf<int> d_gto, d_col_param, d_tab;
+  DBuf<int2> d_dist;                   // hand-out lists of the Jacobian pass (per camera: pose x camera, camera x camera, pose x pose)
+  DBuf<uint4> d_cls_li;                // lane records per camera class
+  DBuf<double> d_Linv, d_zf;
+  int ncls = 0, maxft = 1, k1_grid = 1;
   DBuf<CamMeta> d_cams;
   DBuf<CcEntry> d_cc;
-  DBuf<int2> d_colmap;
   DBuf<double> d_camp[2], d_pose[2];   // current / candidate
   int cur = 0;
   DBuf<double> d_Hff2[2], d_gf2[2], d_Hfc2[2], d_Hcc2[2], d_gc2[2];   // block sets: current point / speculative candidate
   int blk = 0;
-  DBuf<double> d_setup, d_G, d_tile_s, d_Lf, d_cost_f, d_gmax_f, d_xn2_f, d_newcost_f, d_mcc_f, d_dx2_f, d_xn2c_f;
+  DBuf<double> d_setup, d_tile_s, d_Lf, d_cost_f, d_gmax_f, d_xn2_f, d_newcost_f, d_mcc_f, d_dx2_f, d_xn2c_f;
   DBuf<double> d_cc_part, d_cc_sum, d_scale_c, d_scale_f, d_S_part, d_S_sum, d_M, d_yc, d_ysc, d_scal;
   // several ranks: the two all-reduced buffers live in NCCL symmetric-memory windows when the library has them
   double* win_S = nullptr; double* win_cc = nullptr;
@@ -315,7 +314,6 @@ struct mcc_handle {
   long long peer_timeout_cycles = 0;    // k_peer_allreduce gives up after this many SM clocks (MCC_PEER_TIMEOUT_S, default 60 s)
   // iterations queued ahead of their accept / reject decision (solve(): pipelined section)
   LmState* d_state = nullptr;
-  unsigned int* d_ticket = nullptr;     // tile counter of k_tile_normal's persistent warps
   const LmState* st_cur = nullptr;      // what every launch passes: d_state while the pipeline runs, else nullptr
   DecideArgs decide{};                  // st == nullptr: k_scatter_cc takes no decision
   double* d_rec = nullptr;              // [2][LM_REC] decision records
@@ -327,7 +325,7 @@ struct mcc_handle {
   long long it_graph_kernels[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // kernels inside each graph, for the launch count
   double it_graph_key[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};   // the option values baked into the graphs
   double* h_scal = nullptr;            // pinned mirror of d_scal
-  int asm_grid = 0, sy_gx = 0, sy_gy = 0;
+  int sy_gx = 0, sy_gy = 0;
   int sms = 0;
   bool attrs_set = false;
   long long launches = 0, h2d = 0, d2h = 0;
@@ -422,15 +420,13 @@ mcc_status ensure_device(mcc_handle* h) {
   if (!h->h_scal) CU(cudaHostAlloc((void**)&h->h_scal, 33 * sizeof(double), cudaHostAllocDefault));
   if (!h->d_state) {
     CU(cudaMalloc((void**)&h->d_state, sizeof(LmState)));
-    CU(cudaMalloc((void**)&h->d_ticket, sizeof(unsigned int)));
-    CU(cudaMemset(h->d_ticket, 0, sizeof(unsigned int)));   // k_tile_normal leaves it at zero after every launch
     CU(cudaHostAlloc((void**)&h->h_rec, 2 * LM_REC * sizeof(double), cudaHostAllocMapped));   // decide_body writes the records straight to the host
     CU(cudaHostGetDevicePointer((void**)&h->d_rec, h->h_rec, 0));
     for (int i = 0; i < 2; i++) CU(cudaEventCreateWithFlags(&h->ev_rec[i], cudaEventDisableTiming));
   }
   if (!h->attrs_set) {
-    CU((cudaFuncSetAttribute(k_tile_normal<15>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
-    CU((cudaFuncSetAttribute(k_tile_normal<21>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024)));
+    CU((cudaFuncSetAttribute(k_frame_normal<15>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)));
+    CU((cudaFuncSetAttribute(k_frame_normal<21>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)));
     CU(cudaFuncSetAttribute(k_group_setup, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SETUP_SMEM_BYTES));
     CU((cudaFuncSetAttribute(k_schur_syrk<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)));
     CU((cudaFuncSetAttribute(k_schur_syrk<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)));
@@ -620,7 +616,6 @@ mcc_status build_structure(mcc_handle* h) {
     for (int j = 0; j < MAXC; j++) m.red_col[j] = -1;
     for (int j = 0; j < c.nparam(); j++) m.red_col[m.intr_col + j] = h->cam_col[h->intr_off[k] + j];
     if (k > 0) for (int j = 0; j < 6; j++) m.red_col[m.ext_col + j] = h->cam_col[h->ext_off[k] + j];
-    m.lut_off = k * MAXC * MAXC;
     build_units(m, c.n_dist);
     if (c.active) { max_nb = std::max(max_nb, m.nb); max_nblk = std::max(max_nblk, m.nblk); max_red_cols = std::max(max_red_cols, 4 + c.n_dist + 7); }
   }
@@ -632,19 +627,28 @@ mcc_status build_structure(mcc_handle* h) {
         int o;
         if (bi <= bj) o = tri_index(bi, bj, m.nb) * 9 + (i % 3) * 3 + (j % 3);
         else o = tri_index(bj, bi, m.nb) * 9 + (j % 3) * 3 + (i % 3);
-        lut[m.lut_off + i * MAXC + j] = o;
+        lut[k * MAXC * MAXC + i * MAXC + j] = o;
       }
   }
   h->gstride = 9 * max_nblk;
-  // k_tile_normal<RS> works on reduced rows of (4 + n_dist) + 7 columns
+  // k_frame_normal<RS> works on reduced rows of (4 + n_dist) + 7 columns
   h->rowstride = (max_red_cols + 2) / 3 <= 5 ? 15 : 21;
   for (int k = 0; k < ncam; k++) build_lane_map(cm[k], h->rowstride);
-
-  // reduced column -> (camera, local column)
-  std::vector<int2> colmap(std::max(C, 1));
-  for (int k = 0; k < ncam; k++) {
-    for (int j = 0; j < cm[k].r_col; j++) if (cm[k].red_col[j] >= 0) colmap[cm[k].red_col[j]] = make_int2(k, j);   // pose columns carry -1
+  // lane-record classes: the record depends on the unit layout (n_dist) and on the block count of the full layout
+  // (n_dist, extrinsics or not); cameras of one class share a copy in the shared memory of the Jacobian pass
+  std::vector<uint4> cls_li;
+  {
+    std::vector<std::pair<int, int>> classes;
+    for (int k = 0; k < ncam; k++) {
+      const std::pair<int, int> key(h->cams[k].n_dist, k > 0 ? 1 : 0);
+      int ci = -1;
+      for (size_t i = 0; i < classes.size(); i++) if (classes[i] == key) ci = (int)i;
+      if (ci < 0) { ci = (int)classes.size(); classes.push_back(key); cls_li.insert(cls_li.end(), cm[k].lane_info, cm[k].lane_info + 32); }
+      cm[k].cls = ci;
+    }
+    h->ncls = (int)classes.size();
   }
+
   // camera-camera entries
   std::vector<CcEntry> cc;
   for (int k = 0; k < ncam; k++) {
@@ -654,30 +658,38 @@ mcc_status build_structure(mcc_handle* h) {
       if (cm[k].red_col[i] < 0) continue;
       for (int j = i; j < ncc; j++) {
         if (cm[k].red_col[j] < 0) continue;
-        cc.push_back(CcEntry{k, lut[cm[k].lut_off + i * MAXC + j], cm[k].red_col[i], cm[k].red_col[j]});
+        cc.push_back(CcEntry{k, lut[k * MAXC * MAXC + i * MAXC + j], cm[k].red_col[i], cm[k].red_col[j]});
       }
-      cc.push_back(CcEntry{k, lut[cm[k].lut_off + i * MAXC + cm[k].r_col], cm[k].red_col[i], -1});
+      cc.push_back(CcEntry{k, lut[k * MAXC * MAXC + i * MAXC + cm[k].r_col], cm[k].red_col[i], -1});
     }
   }
   h->E = (int)cc.size();
-  // direct gather tables for the frame blocks
-  std::vector<int> hff_tab((size_t)42 * ncam, 0);
-  for (int ent = 0; ent < 42; ent++) {
-    const int a = ent / 7, b = ent % 7;
-    for (int k = 0; k < ncam; k++) hff_tab[(size_t)ent * ncam + k] = lut[cm[k].lut_off + (cm[k].pose_col + a) * MAXC + (b < 6 ? cm[k].pose_col + b : cm[k].r_col)];
-  }
-  std::vector<int2> hfc_tab((size_t)6 * std::max(C, 1), make_int2(0, 0));
-  for (int a = 0; a < 6; a++)
-    for (int c = 0; c < C; c++) {
-      const int2 cmap = colmap[c];
-      hfc_tab[(size_t)a * C + c] = make_int2(cmap.x, lut[cm[cmap.x].lut_off + cmap.y * MAXC + cm[cmap.x].pose_col + a]);
-    }
   // entry range of every camera in cc[] (entries were pushed camera by camera)
   std::vector<int> cc_e0(ncam + 1, 0);
   {
     size_t e = 0;
     for (int k = 0; k < ncam; k++) { cc_e0[k] = (int)e; while (e < cc.size() && cc[e].cam == k) e++; }
     cc_e0[ncam] = (int)e;
+  }
+  // hand-out lists of the Jacobian pass: where the entries of a camera's expanded Gram record (offsets by `lut`) go.
+  //   pose x camera columns  -> H_fc[frame][a * C + reduced column]
+  //   camera x camera (+ camera gradient) entries -> index into the camera-camera entry vector
+  //   pose x pose (+ pose gradient) -> entry a * 7 + b of the frame's 6 x 7 block (b == 6: gradient), in this order
+  std::vector<int2> dist;
+  for (int k = 0; k < ncam; k++) {
+    CamMeta& m = cm[k];
+    const int* L = &lut[(size_t)k * MAXC * MAXC];
+    m.dist_off = (int)dist.size();
+    for (int a = 0; a < 6; a++)
+      for (int j = 0; j < m.r_col; j++)
+        if (m.red_col[j] >= 0) dist.push_back(make_int2(L[j * MAXC + m.pose_col + a], a * C + m.red_col[j]));
+    m.n_hfc = (int)dist.size() - m.dist_off;
+    for (int e = cc_e0[k]; e < cc_e0[k + 1]; e++) dist.push_back(make_int2(cc[e].gram_off, e));
+    m.n_cc = cc_e0[k + 1] - cc_e0[k];
+    for (int ent = 0; ent < 42; ent++) {
+      const int a = ent / 7, b2 = ent % 7;
+      dist.push_back(make_int2(L[(m.pose_col + a) * MAXC + (b2 < 6 ? m.pose_col + b2 : m.r_col)], ent));
+    }
   }
 
   // observation offsets, active frames, tiles
@@ -726,27 +738,8 @@ mcc_status build_structure(mcc_handle* h) {
   }
   gto[h->ngroups] = (int)tiles.size();
   h->ntiles = (int)tiles.size();
-  // per-camera tile lists (tile order = frame order) cut into chunks for the camera-camera reduction
-  std::vector<int> cam_tiles;
-  std::vector<CcChunk> cc_chunks;
-  std::vector<int> cam_chunk0(ncam + 1, 0);
-  h->cc_maxne = 1;
-  {
-    std::vector<std::vector<int>> per(ncam);
-    for (int t = 0; t < h->ntiles; t++) per[tiles[t].group % ncam].push_back(t);
-    for (int k = 0; k < ncam; k++) {
-      cam_chunk0[k] = (int)cc_chunks.size();
-      const int ne = cc_e0[k + 1] - cc_e0[k];
-      h->cc_maxne = std::max(h->cc_maxne, ne);
-      if (ne == 0) continue;
-      const int first = (int)cam_tiles.size();
-      cam_tiles.insert(cam_tiles.end(), per[k].begin(), per[k].end());
-      for (int o = 0; o < (int)per[k].size(); o += CC_CHUNK)
-        cc_chunks.push_back(CcChunk{k, first + o, std::min(CC_CHUNK, (int)per[k].size() - o), cc_e0[k], ne});
-    }
-    cam_chunk0[ncam] = (int)cc_chunks.size();
-  }
-  h->ncc_chunks = (int)cc_chunks.size();
+  h->maxft = 1;
+  for (int sl = 0; sl < h->nslots; sl++) h->maxft = std::max(h->maxft, gto[(size_t)(sl + 1) * ncam] - gto[(size_t)sl * ncam]);
 
   const int NT = (C + 1 + SY_T - 1) / SY_T;
   h->npairs = NT * (NT + 1) / 2;
@@ -755,7 +748,15 @@ mcc_status build_structure(mcc_handle* h) {
   if (h->sms <= 0) CU(cudaDeviceGetAttribute(&h->sms, cudaDevAttrMultiProcessorCount, h->device));
   const int sms = h->sms;
   h->sy_gx = std::max(1, std::min((h->nslots + SY_FB - 1) / SY_FB, std::max(1, (2 * sms) / h->sy_gy)));
-  h->asm_grid = 1;
+  // the Jacobian pass: persistent CTAs, as many as fit at once (shared memory: rows of 4 warps + the frame's tile Grams)
+  {
+    const size_t smem = k1_smem_bytes(h->rowstride, ncam, h->maxft);
+    if (smem > 200 * 1024) return fail(h, MCC_ERR_TOO_LARGE, "a frame with %d tiles needs %zu bytes of shared memory in the Jacobian pass", h->maxft, smem);
+    int occ = 0;
+    if (h->rowstride == 15) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_frame_normal<15>, K1_WARPS * 32, smem));
+    else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_frame_normal<21>, K1_WARPS * 32, smem));
+    h->k1_grid = std::max(1, std::min(std::max(h->nslots, 1), std::max(occ, 1) * sms));
+  }
 
   // upload structure
   auto up = [&](auto& buf, const auto& vec) -> cudaError_t {
@@ -766,29 +767,21 @@ mcc_status build_structure(mcc_handle* h) {
     return cudaMemcpyAsync(buf.p, vec.data(), vec.size() * sizeof(vec[0]), cudaMemcpyHostToDevice, h->stream);
   };
   CU(up(h->d_cams, cm));
-  CU(up(h->d_lut, lut));
-  CU(up(h->d_colmap, colmap));
   CU(up(h->d_cc, cc));
-  CU(up(h->d_hff_tab, hff_tab));
-  CU(up(h->d_hfc_tab, hfc_tab));
-  CU(up(h->d_cam_tiles, cam_tiles));
-  CU(up(h->d_cc_chunks, cc_chunks));
-  cam_chunk0.insert(cam_chunk0.end(), cc_e0.begin(), cc_e0.end());   // [ncam+1] chunk ranges, then [ncam+1] entry ranges
-  CU(up(h->d_cam_chunk0, cam_chunk0));
-  CU(h->d_w_f.reserve(std::max(h->nslots, 1)));
+  CU(up(h->d_dist, dist));
+  CU(up(h->d_cls_li, cls_li));
   CU(h->d_Linv.reserve((size_t)std::max(h->nslots, 1) * 6)); CU(h->d_zf.reserve((size_t)std::max(h->nslots, 1) * 6));
   CU(up(h->d_tiles, tiles));
   CU(up(h->d_gto, gto));
   CU(up(h->d_col_param, h->col_param));
   const size_t ns = std::max(h->nslots, 1);
   CU(h->d_setup.reserve((size_t)std::max(h->ngroups, 1) * SETUP_STRIDE));
-  CU(h->d_G.reserve((size_t)std::max(h->ntiles, 1) * h->gstride));
   CU(h->d_tile_s.reserve(std::max(h->ntiles, 1)));
   for (int b = 0; b < 2; b++) { CU(h->d_Hff2[b].reserve(ns * 36)); CU(h->d_gf2[b].reserve(ns * 6)); CU(h->d_Hfc2[b].reserve(ns * 6 * std::max(C, 1))); }
   CU(h->d_Lf.reserve(ns * 36));
   CU(h->d_cost_f.reserve(ns)); CU(h->d_gmax_f.reserve(ns)); CU(h->d_xn2_f.reserve(ns)); CU(h->d_newcost_f.reserve(ns));
   CU(h->d_mcc_f.reserve(ns)); CU(h->d_dx2_f.reserve(ns)); CU(h->d_xn2c_f.reserve(ns));
-  CU(h->d_cc_part.reserve((size_t)std::max(h->ncc_chunks, 1) * h->cc_maxne)); CU(h->d_cc_sum.reserve((size_t)h->E + COMM_SCAL + 2 * 64));
+  CU(h->d_cc_part.reserve((size_t)h->k1_grid * std::max(h->E, 1))); CU(h->d_cc_sum.reserve((size_t)h->E + COMM_SCAL + 2 * 64));
   for (int b = 0; b < 2; b++) { CU(h->d_Hcc2[b].reserve((size_t)std::max(C, 1) * std::max(C, 1))); CU(h->d_gc2[b].reserve(std::max(C, 1))); }
   CU(h->d_scale_c.reserve(std::max(C, 1))); CU(h->d_scale_f.reserve(ns * 6));
   CU(h->d_S_part.reserve((size_t)h->sy_gx * h->npairs * SY_T * SY_T)); CU(h->d_S_sum.reserve((size_t)h->npairs * SY_T * SY_T));
@@ -1085,31 +1078,18 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
   double* tail = cc_sum_buf(h) + h->E;
   // the per-rank slots of the other ranks have to be zero; on one rank every entry is written (k_reduce_misc)
   if (multi) CU(cudaMemsetAsync(cc_sum_buf(h), 0, ((size_t)h->E + COMM_SCAL + 2 * 64) * sizeof(double), h->stream));
-  ST(launch_setup(h, which));
-  if (h->ntiles) {
-    const size_t smem = (size_t)K1_WARPS * (k1_rows_doubles(h->rowstride) + K1_EXTRA) * sizeof(double);
-    // persistent warps: four CTAs per SM (registers), each warp draws tiles from d_ticket
-    const int grid = std::min((h->ntiles + K1_WARPS - 1) / K1_WARPS, 4 * std::max(h->sms, 1));
-    KScope ks(h, KC_TILE_NORMAL);
-#define MCC_LAUNCH_TILE_NORMAL(RS)                                                                                                          \
-    k_tile_normal<RS><<<grid, K1_WARPS * 32, smem, h->stream>>>(h->ntiles, h->ncam(), h->d_tiles.p, h->d_cams.p, h->d_setup.p, h->d_camp[which].p, \
-                                                                      h->d_X.p, h->d_Y.p, h->d_Z.p, h->d_U.p, h->d_V.p, h->d_mask.p, h->d_G.p, h->gstride, h->d_tile_s.p, h->d_ticket, h->st_cur)
-    if (h->rowstride == 15) MCC_LAUNCH_TILE_NORMAL(15);
-    else MCC_LAUNCH_TILE_NORMAL(21);
-#undef MCC_LAUNCH_TILE_NORMAL
-    CU(cudaGetLastError());
-  }
   if (h->nslots) {
-    KScope ks(h, KC_ASSEMBLE);
-    k_frame_blocks<<<h->nslots, 128, 0, h->stream>>>(h->nslots, h->ncam(), h->C, h->d_gto.p, h->d_hff_tab.p, h->d_hfc_tab.p, h->d_G.p, h->gstride,
-                                                     h->d_tile_s.p, h->d_pose[which].p, use_loss, h->d_Hff2[bo].p, h->d_gf2[bo].p, h->d_Hfc2[bo].p, h->d_cost_f.p,
-                                                     h->d_gmax_f.p, h->d_xn2_f.p, h->d_w_f.p, h->st_cur);
-  }
-  CU(cudaGetLastError());
-  if (h->E && h->ncc_chunks) {
-    KScope ks(h, KC_ASSEMBLE);
-    k_cc_partial<<<h->ncc_chunks, 128, 0, h->stream>>>(h->ncam(), h->d_cc_chunks.p, h->d_cam_tiles.p, h->d_tiles.p, h->d_cc.p, h->d_w_f.p, h->d_G.p,
-                                                       h->gstride, h->cc_maxne, h->d_cc_part.p, h->st_cur);
+    K1Args ka;
+    ka.nslots = h->nslots; ka.ncam = h->ncam(); ka.C = h->C; ka.maxft = h->maxft; ka.E = h->E; ka.use_loss = use_loss; ka.ncls = h->ncls; ka.gstride = h->gstride;
+    ka.tiles = h->d_tiles.p; ka.gto = h->d_gto.p; ka.cams = h->d_cams.p; ka.cls_lane_info = h->d_cls_li.p; ka.dist = h->d_dist.p;
+    ka.camp = h->d_camp[which].p; ka.pose = h->d_pose[which].p;
+    ka.oX = h->d_X.p; ka.oY = h->d_Y.p; ka.oZ = h->d_Z.p; ka.oU = h->d_U.p; ka.oV = h->d_V.p; ka.omask = h->d_mask.p;
+    ka.Hff = h->d_Hff2[bo].p; ka.gf = h->d_gf2[bo].p; ka.Hfc = h->d_Hfc2[bo].p; ka.cost_f = h->d_cost_f.p; ka.gmax_f = h->d_gmax_f.p; ka.xn2_f = h->d_xn2_f.p;
+    ka.cc_part = h->d_cc_part.p; ka.st = h->st_cur;
+    const size_t smem = k1_smem_bytes(h->rowstride, h->ncam(), h->maxft);
+    KScope ks(h, KC_TILE_NORMAL);
+    if (h->rowstride == 15) k_frame_normal<15><<<h->k1_grid, K1_WARPS * 32, smem, h->stream>>>(ka);
+    else k_frame_normal<21><<<h->k1_grid, K1_WARPS * 32, smem, h->stream>>>(ka);
   }
   CU(cudaGetLastError());
   ReduceJobs jobs;
@@ -1120,10 +1100,9 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
   for (int i = 0; i < nextra && i < 5; i++) jobs.j[3 + i] = extra[i];
   {
     KScope ks(h, KC_REDUCE);
-    const int ncc = h->E ? h->ncam() : 0;
-    const size_t smem = std::max((size_t)CCR_S * h->cc_maxne, (size_t)1024) * sizeof(double);
-    k_reduce_misc<<<ncc + 3 + nextra, 1024, smem, h->stream>>>(ncc, h->ncam(), h->d_cam_chunk0.p, h->d_cc_chunks.p, h->cc_maxne, h->d_cc_part.p, cc_sum_buf(h), jobs,
-                                                               h->nslots, h->d_scal.p, h->st_cur);
+    // camera-camera entries: one partial row per CTA of the Jacobian pass (no rows at all on a rank without frames)
+    const int ncc = (h->E + CCR_E - 1) / CCR_E;
+    k_reduce_misc<<<ncc + 3 + nextra, 1024, 0, h->stream>>>(ncc, h->E, h->nslots ? h->k1_grid : 0, h->d_cc_part.p, cc_sum_buf(h), jobs, h->nslots, h->d_scal.p, h->st_cur);
   }
   CU(cudaGetLastError());
   if (multi) {
@@ -1503,17 +1482,16 @@ void mcc_destroy(mcc_handle* h) {
   if (h->comm && nccl().has_windows()) free_comm_windows(h);
   if (h->comm && nccl().CommDestroy) nccl().CommDestroy(h->comm);
   DBuf<double>* dd[] = {&h->d_aos_w, &h->d_aos_i, &h->d_X, &h->d_Y, &h->d_Z, &h->d_U, &h->d_V, &h->d_res, &h->d_camp[0], &h->d_camp[1], &h->d_pose[0], &h->d_pose[1],
-                        &h->d_setup, &h->d_G, &h->d_tile_s, &h->d_Hff2[0], &h->d_Hff2[1], &h->d_gf2[0], &h->d_gf2[1], &h->d_Hfc2[0], &h->d_Hfc2[1], &h->d_Lf, &h->d_cost_f, &h->d_gmax_f, &h->d_xn2_f, &h->d_newcost_f,
+                        &h->d_setup, &h->d_tile_s, &h->d_Hff2[0], &h->d_Hff2[1], &h->d_gf2[0], &h->d_gf2[1], &h->d_Hfc2[0], &h->d_Hfc2[1], &h->d_Lf, &h->d_cost_f, &h->d_gmax_f, &h->d_xn2_f, &h->d_newcost_f,
                         &h->d_mcc_f, &h->d_dx2_f, &h->d_xn2c_f, &h->d_cc_part, &h->d_cc_sum, &h->d_Hcc2[0], &h->d_Hcc2[1], &h->d_gc2[0], &h->d_gc2[1], &h->d_scale_c, &h->d_scale_f, &h->d_S_part,
                         &h->d_S_sum, &h->d_M, &h->d_yc, &h->d_ysc, &h->d_scal};
   for (auto* b : dd) b->release();
-  h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_tab.release(); h->d_lut.release(); h->d_col_param.release(); 
-  h->d_cams.release(); h->d_cc.release(); h->d_colmap.release(); h->d_hff_tab.release(); h->d_hfc_tab.release();
-  h->d_cam_tiles.release(); h->d_cam_chunk0.release(); h->d_cc_chunks.release(); h->d_w_f.release(); h->d_Linv.release(); h->d_zf.release();
+  h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_tab.release(); h->d_col_param.release(); h->d_dist.release(); h->d_cls_li.release();
+  h->d_cams.release(); h->d_cc.release(); h->d_Linv.release(); h->d_zf.release();
   h->world.release(); h->image.release();
   if (h->h_scal) cudaFreeHost(h->h_scal);
   drop_iteration_graphs(h);
-  if (h->d_state) { cudaFree(h->d_state); cudaFree(h->d_ticket); cudaFreeHost(h->h_rec); for (int i = 0; i < 2; i++) cudaEventDestroy(h->ev_rec[i]); }
+  if (h->d_state) { cudaFree(h->d_state); cudaFreeHost(h->h_rec); for (int i = 0; i < 2; i++) cudaEventDestroy(h->ev_rec[i]); }
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   for (KPending& pe : h->ev_pending) { cudaEventDestroy(pe.a); cudaEventDestroy(pe.b); }
   if (h->tm_a) { cudaEventDestroy(h->tm_a); cudaEventDestroy(h->tm_b); }
