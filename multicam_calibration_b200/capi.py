@@ -18,7 +18,7 @@ import numpy as np
 from .rig import Camera, Rig
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmcc.so")
+LIB_PATH = os.environ.get("MCC_LIB") or os.path.join(_HERE, "libmcc.so")   # MCC_LIB: another build of the same library (kernel experiments)
 
 MAX_TRACE = 256
 UNIQUE_ID_BYTES = 128

@@ -462,7 +462,6 @@ void init_params(mcc_handle* h) {
   h->params_dirty = true;
 }
 
-int tri_index(int bi, int bj, int nb) { return bi * nb - bi * (bi - 1) / 2 + (bj - bi); }
 
 // Everything that depends on cameras, flags, frame list and masks: reduced column maps
 // (calibrator.cpp:510-521), frames with residual blocks (calibrator.cpp:482-485), tiles.
@@ -575,6 +574,15 @@ static void build_lane_map(CamMeta& m, int rs) {
   }
 }
 
+// (a, b) of a camera's full column layout [ext | pose | intr | r] as the Jacobian pass wants it: a | b << 8 with the
+// geometry column (ext / pose) first when only one of the two is geometry, and a <= b when both are
+int ab_code(const CamMeta& m, int i, int j) {
+  const int ng = m.intr_col;   // geometry columns come first
+  if (i < ng && j < ng) { if (i > j) std::swap(i, j); }
+  else if (j < ng) std::swap(i, j);
+  return i | (j << 8);
+}
+
 mcc_status build_structure(mcc_handle* h) {
   const int ncam = h->ncam();
   const int F = h->nframes;
@@ -594,9 +602,8 @@ mcc_status build_structure(mcc_handle* h) {
   h->C = (int)h->col_param.size();
   const int C = h->C;
 
-  // camera metadata + Gram lookup tables
+  // camera metadata
   std::vector<CamMeta> cm(ncam);
-  std::vector<int> lut((size_t)ncam * MAXC * MAXC, 0);
   int max_nb = 1, max_nblk = 1, max_red_cols = 11;
   for (int k = 0; k < ncam; k++) {
     const CamHost& c = h->cams[k];
@@ -618,17 +625,6 @@ mcc_status build_structure(mcc_handle* h) {
     if (k > 0) for (int j = 0; j < 6; j++) m.red_col[m.ext_col + j] = h->cam_col[h->ext_off[k] + j];
     build_units(m, c.n_dist);
     if (c.active) { max_nb = std::max(max_nb, m.nb); max_nblk = std::max(max_nblk, m.nblk); max_red_cols = std::max(max_red_cols, 4 + c.n_dist + 7); }
-  }
-  for (int k = 0; k < ncam; k++) {
-    const CamMeta& m = cm[k];
-    for (int i = 0; i < m.ncols; i++)
-      for (int j = 0; j < m.ncols; j++) {
-        const int bi = i / 3, bj = j / 3;
-        int o;
-        if (bi <= bj) o = tri_index(bi, bj, m.nb) * 9 + (i % 3) * 3 + (j % 3);
-        else o = tri_index(bj, bi, m.nb) * 9 + (j % 3) * 3 + (i % 3);
-        lut[k * MAXC * MAXC + i * MAXC + j] = o;
-      }
   }
   h->gstride = 9 * max_nblk;
   // k_frame_normal<RS> works on reduced rows of (4 + n_dist) + 7 columns
@@ -658,9 +654,9 @@ mcc_status build_structure(mcc_handle* h) {
       if (cm[k].red_col[i] < 0) continue;
       for (int j = i; j < ncc; j++) {
         if (cm[k].red_col[j] < 0) continue;
-        cc.push_back(CcEntry{k, lut[k * MAXC * MAXC + i * MAXC + j], cm[k].red_col[i], cm[k].red_col[j]});
+        cc.push_back(CcEntry{k, ab_code(cm[k], i, j), cm[k].red_col[i], cm[k].red_col[j]});
       }
-      cc.push_back(CcEntry{k, lut[k * MAXC * MAXC + i * MAXC + cm[k].r_col], cm[k].red_col[i], -1});
+      cc.push_back(CcEntry{k, ab_code(cm[k], i, cm[k].r_col), cm[k].red_col[i], -1});
     }
   }
   h->E = (int)cc.size();
@@ -671,24 +667,24 @@ mcc_status build_structure(mcc_handle* h) {
     for (int k = 0; k < ncam; k++) { cc_e0[k] = (int)e; while (e < cc.size() && cc[e].cam == k) e++; }
     cc_e0[ncam] = (int)e;
   }
-  // hand-out lists of the Jacobian pass: where the entries of a camera's expanded Gram record (offsets by `lut`) go.
+  // hand-out lists of the Jacobian pass: which entries (a, b) of a camera's Gram matrix over the full column layout
+  // [ext | pose | intr | r] go where (ab_code packs and orders the pair the way the kernel's `entry` expects it).
   //   pose x camera columns  -> H_fc[frame][a * C + reduced column]
   //   camera x camera (+ camera gradient) entries -> index into the camera-camera entry vector
   //   pose x pose (+ pose gradient) -> entry a * 7 + b of the frame's 6 x 7 block (b == 6: gradient), in this order
   std::vector<int2> dist;
   for (int k = 0; k < ncam; k++) {
     CamMeta& m = cm[k];
-    const int* L = &lut[(size_t)k * MAXC * MAXC];
     m.dist_off = (int)dist.size();
     for (int a = 0; a < 6; a++)
       for (int j = 0; j < m.r_col; j++)
-        if (m.red_col[j] >= 0) dist.push_back(make_int2(L[j * MAXC + m.pose_col + a], a * C + m.red_col[j]));
+        if (m.red_col[j] >= 0) dist.push_back(make_int2(ab_code(m, j, m.pose_col + a), a * C + m.red_col[j]));
     m.n_hfc = (int)dist.size() - m.dist_off;
     for (int e = cc_e0[k]; e < cc_e0[k + 1]; e++) dist.push_back(make_int2(cc[e].gram_off, e));
     m.n_cc = cc_e0[k + 1] - cc_e0[k];
     for (int ent = 0; ent < 42; ent++) {
       const int a = ent / 7, b2 = ent % 7;
-      dist.push_back(make_int2(L[(m.pose_col + a) * MAXC + (b2 < 6 ? m.pose_col + b2 : m.r_col)], ent));
+      dist.push_back(make_int2(ab_code(m, m.pose_col + a, b2 < 6 ? m.pose_col + b2 : m.r_col), ent));
     }
   }
 
