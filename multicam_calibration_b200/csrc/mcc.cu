@@ -299,6 +299,7 @@ struct mcc_handle {
   int cur = 0;
   DBuf<double> d_Hff2[2], d_gf2[2], d_Hfc2[2], d_Hcc2[2], d_gc2[2];   // block sets: current point / speculative candidate
   int blk = 0;
+  DBuf<double> d_frot, d_camrec;       // rotation records of the Jacobian pass (k_rot_setup)
   DBuf<double> d_setup, d_tile_s, d_Lf, d_cost_f, d_gmax_f, d_xn2_f, d_newcost_f, d_mcc_f, d_dx2_f, d_xn2c_f;
   DBuf<double> d_cc_part, d_cc_sum, d_scale_c, d_scale_f, d_S_part, d_S_sum, d_M, d_yc, d_ysc, d_scal;
   // several ranks: the two all-reduced buffers live in NCCL symmetric-memory windows when the library has them
@@ -772,6 +773,7 @@ mcc_status build_structure(mcc_handle* h) {
   CU(up(h->d_col_param, h->col_param));
   const size_t ns = std::max(h->nslots, 1);
   CU(h->d_setup.reserve((size_t)std::max(h->ngroups, 1) * SETUP_STRIDE));
+  CU(h->d_frot.reserve(ns * K1_FROT)); CU(h->d_camrec.reserve((size_t)std::max(ncam, 1) * K1_CAMREC));
   CU(h->d_tile_s.reserve(std::max(h->ntiles, 1)));
   for (int b = 0; b < 2; b++) { CU(h->d_Hff2[b].reserve(ns * 36)); CU(h->d_gf2[b].reserve(ns * 6)); CU(h->d_Hfc2[b].reserve(ns * 6 * std::max(C, 1))); }
   CU(h->d_Lf.reserve(ns * 36));
@@ -1078,11 +1080,16 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
     K1Args ka;
     ka.nslots = h->nslots; ka.ncam = h->ncam(); ka.C = h->C; ka.maxft = h->maxft; ka.E = h->E; ka.use_loss = use_loss; ka.ncls = h->ncls; ka.gstride = h->gstride;
     ka.tiles = h->d_tiles.p; ka.gto = h->d_gto.p; ka.cams = h->d_cams.p; ka.cls_lane_info = h->d_cls_li.p; ka.dist = h->d_dist.p;
-    ka.camp = h->d_camp[which].p; ka.pose = h->d_pose[which].p;
+    ka.camrec = h->d_camrec.p; ka.frot = h->d_frot.p; ka.pose = h->d_pose[which].p;
     ka.oX = h->d_X.p; ka.oY = h->d_Y.p; ka.oZ = h->d_Z.p; ka.oU = h->d_U.p; ka.oV = h->d_V.p; ka.omask = h->d_mask.p;
     ka.Hff = h->d_Hff2[bo].p; ka.gf = h->d_gf2[bo].p; ka.Hfc = h->d_Hfc2[bo].p; ka.cost_f = h->d_cost_f.p; ka.gmax_f = h->d_gmax_f.p; ka.xn2_f = h->d_xn2_f.p;
     ka.cc_part = h->d_cc_part.p; ka.st = h->st_cur;
     const size_t smem = k1_smem_bytes(h->rowstride, h->ncam(), h->maxft);
+    {
+      KScope ks(h, KC_SETUP);
+      k_rot_setup<<<(h->nslots + h->ncam() + 127) / 128, 128, 0, h->stream>>>(h->nslots, h->ncam(), h->d_cams.p, h->d_camp[which].p, h->d_pose[which].p, h->d_frot.p,
+                                                                              h->d_camrec.p, h->st_cur);
+    }
     KScope ks(h, KC_TILE_NORMAL);
     if (h->rowstride == 15) k_frame_normal<15><<<h->k1_grid, K1_WARPS * 32, smem, h->stream>>>(ka);
     else k_frame_normal<21><<<h->k1_grid, K1_WARPS * 32, smem, h->stream>>>(ka);
@@ -1478,7 +1485,7 @@ void mcc_destroy(mcc_handle* h) {
   if (h->comm && nccl().has_windows()) free_comm_windows(h);
   if (h->comm && nccl().CommDestroy) nccl().CommDestroy(h->comm);
   DBuf<double>* dd[] = {&h->d_aos_w, &h->d_aos_i, &h->d_X, &h->d_Y, &h->d_Z, &h->d_U, &h->d_V, &h->d_res, &h->d_camp[0], &h->d_camp[1], &h->d_pose[0], &h->d_pose[1],
-                        &h->d_setup, &h->d_tile_s, &h->d_Hff2[0], &h->d_Hff2[1], &h->d_gf2[0], &h->d_gf2[1], &h->d_Hfc2[0], &h->d_Hfc2[1], &h->d_Lf, &h->d_cost_f, &h->d_gmax_f, &h->d_xn2_f, &h->d_newcost_f,
+                        &h->d_setup, &h->d_frot, &h->d_camrec, &h->d_tile_s, &h->d_Hff2[0], &h->d_Hff2[1], &h->d_gf2[0], &h->d_gf2[1], &h->d_Hfc2[0], &h->d_Hfc2[1], &h->d_Lf, &h->d_cost_f, &h->d_gmax_f, &h->d_xn2_f, &h->d_newcost_f,
                         &h->d_mcc_f, &h->d_dx2_f, &h->d_xn2c_f, &h->d_cc_part, &h->d_cc_sum, &h->d_Hcc2[0], &h->d_Hcc2[1], &h->d_gc2[0], &h->d_gc2[1], &h->d_scale_c, &h->d_scale_f, &h->d_S_part,
                         &h->d_S_sum, &h->d_M, &h->d_yc, &h->d_ysc, &h->d_scal};
   for (auto* b : dd) b->release();
