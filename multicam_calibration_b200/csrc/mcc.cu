@@ -577,11 +577,25 @@ static void build_lane_map(CamMeta& m, int rs) {
 
 // (a, b) of a camera's full column layout [ext | pose | intr | r] as the Jacobian pass wants it: a | b << 8 with the
 // geometry column (ext / pose) first when only one of the two is geometry, and a <= b when both are
-int ab_code(const CamMeta& m, int i, int j) {
+int ab_code(const CamMeta& m, int i, int j, int rs) {
   const int ng = m.intr_col;   // geometry columns come first
+#if MCC_K1_DIRECT
+  // geometry x geometry is computed in the kernel (-1 - (a | b << 8), a <= b); everything else already sits in the warp's
+  // shared memory and is coded by its offset: geometry x other = Y[reduced column of the other][geometry column] (Y
+  // follows the reduced Gram matrix Gs), other x other = Gs[reduced][reduced]
+  if (i < ng && j < ng) { if (i > j) std::swap(i, j); return -1 - (i | (j << 8)); }
+  if (j < ng) std::swap(i, j);
+  const int nk = 4 + m.nd;
+  const int rj = j < m.r_col ? j - ng : nk + 6;
+  if (i < ng) return k1_gsrows(rs) * k1_gsld(rs) + rj * 12 + i;
+  const int ri = i < m.r_col ? i - ng : nk + 6;
+  return ri * k1_gsld(rs) + rj;
+#else
+  (void)rs;
   if (i < ng && j < ng) { if (i > j) std::swap(i, j); }
   else if (j < ng) std::swap(i, j);
   return i | (j << 8);
+#endif
 }
 
 mcc_status build_structure(mcc_handle* h) {
@@ -655,9 +669,9 @@ mcc_status build_structure(mcc_handle* h) {
       if (cm[k].red_col[i] < 0) continue;
       for (int j = i; j < ncc; j++) {
         if (cm[k].red_col[j] < 0) continue;
-        cc.push_back(CcEntry{k, ab_code(cm[k], i, j), cm[k].red_col[i], cm[k].red_col[j]});
+        cc.push_back(CcEntry{k, ab_code(cm[k], i, j, h->rowstride), cm[k].red_col[i], cm[k].red_col[j]});
       }
-      cc.push_back(CcEntry{k, ab_code(cm[k], i, cm[k].r_col), cm[k].red_col[i], -1});
+      cc.push_back(CcEntry{k, ab_code(cm[k], i, cm[k].r_col, h->rowstride), cm[k].red_col[i], -1});
     }
   }
   h->E = (int)cc.size();
@@ -679,13 +693,14 @@ mcc_status build_structure(mcc_handle* h) {
     m.dist_off = (int)dist.size();
     for (int a = 0; a < 6; a++)
       for (int j = 0; j < m.r_col; j++)
-        if (m.red_col[j] >= 0) dist.push_back(make_int2(ab_code(m, j, m.pose_col + a), a * C + m.red_col[j]));
+        if (m.red_col[j] >= 0) dist.push_back(make_int2(ab_code(m, j, m.pose_col + a, h->rowstride), a * C + m.red_col[j]));
     m.n_hfc = (int)dist.size() - m.dist_off;
     for (int e = cc_e0[k]; e < cc_e0[k + 1]; e++) dist.push_back(make_int2(cc[e].gram_off, e));
     m.n_cc = cc_e0[k + 1] - cc_e0[k];
+    m.e0 = cc_e0[k];
     for (int ent = 0; ent < 42; ent++) {
       const int a = ent / 7, b2 = ent % 7;
-      dist.push_back(make_int2(ab_code(m, m.pose_col + a, b2 < 6 ? m.pose_col + b2 : m.r_col), ent));
+      dist.push_back(make_int2(ab_code(m, m.pose_col + a, b2 < 6 ? m.pose_col + b2 : m.r_col, h->rowstride), ent));
     }
   }
 
