@@ -288,7 +288,7 @@ struct mcc_handle {
   DBuf<double> d_aos_w, d_aos_i, d_X, d_Y, d_Z, d_U, d_V, d_res;
   DBuf<uint8_t> d_mask;
   DBuf<Tile> d_tiles;
-  DBuf<int> d_gto, d_col_param, d_tab;
+  DBuf<int> d_gto, d_col_param, d_tab, d_gs_tab;
   DBuf<int2> d_dist;                   // hand-out lists of the Jacobian pass (per camera: pose x camera, camera x camera, pose x pose)
   DBuf<uint4> d_cls_li;                // lane records per camera class
   DBuf<double> d_Linv, d_zf;
@@ -575,28 +575,22 @@ static void build_lane_map(CamMeta& m, int rs) {
   }
 }
 
-// (a, b) of a camera's full column layout [ext | pose | intr | r] as the Jacobian pass wants it: a | b << 8 with the
-// geometry column (ext / pose) first when only one of the two is geometry, and a <= b when both are
+// Entry (i, j) of a camera's Gram matrix over the full column layout [ext | pose | intr | r] as the hand-out phase of
+// the Jacobian pass finds it (kernels.cuh): geometry x geometry (ext / pose columns) is computed there and coded
+// a | b << 8 with a <= b; everything else already sits in the warp's shared memory and is coded by its offset from
+// `rows`: geometry x other = Y[reduced column of the other][geometry column] (Y follows the reduced Gram matrix Gs),
+// other x other = Gs[reduced][reduced]; the reduced column of intrinsic c is c - ng, of the residual column n_k + 6.
 int ab_code(const CamMeta& m, int i, int j, int rs) {
   const int ng = m.intr_col;   // geometry columns come first
-#if MCC_K1_DIRECT
-  // geometry x geometry is computed in the kernel (-1 - (a | b << 8), a <= b); everything else already sits in the warp's
-  // shared memory and is coded by its offset: geometry x other = Y[reduced column of the other][geometry column] (Y
-  // follows the reduced Gram matrix Gs), other x other = Gs[reduced][reduced]
-  if (i < ng && j < ng) { if (i > j) std::swap(i, j); return -1 - (i | (j << 8)); }
+  if (i < ng && j < ng) { if (i > j) std::swap(i, j); return i | (j << 8); }
   if (j < ng) std::swap(i, j);
   const int nk = 4 + m.nd;
   const int rj = j < m.r_col ? j - ng : nk + 6;
   if (i < ng) return k1_gsrows(rs) * k1_gsld(rs) + rj * 12 + i;
   const int ri = i < m.r_col ? i - ng : nk + 6;
   return ri * k1_gsld(rs) + rj;
-#else
-  (void)rs;
-  if (i < ng && j < ng) { if (i > j) std::swap(i, j); }
-  else if (j < ng) std::swap(i, j);
-  return i | (j << 8);
-#endif
 }
+inline bool ab_is_geo(const CamMeta& m, int i, int j) { return i < m.intr_col && j < m.intr_col; }
 
 mcc_status build_structure(mcc_handle* h) {
   const int ncam = h->ncam();
@@ -648,13 +642,28 @@ mcc_status build_structure(mcc_handle* h) {
   // lane-record classes: the record depends on the unit layout (n_dist) and on the block count of the full layout
   // (n_dist, extrinsics or not); cameras of one class share a copy in the shared memory of the Jacobian pass
   std::vector<uint4> cls_li;
+  std::vector<int> gs_tab;
   {
     std::vector<std::pair<int, int>> classes;
     for (int k = 0; k < ncam; k++) {
       const std::pair<int, int> key(h->cams[k].n_dist, k > 0 ? 1 : 0);
       int ci = -1;
       for (size_t i = 0; i < classes.size(); i++) if (classes[i] == key) ci = (int)i;
-      if (ci < 0) { ci = (int)classes.size(); classes.push_back(key); cls_li.insert(cls_li.end(), cm[k].lane_info, cm[k].lane_info + 32); }
+      if (ci < 0) {
+        ci = (int)classes.size(); classes.push_back(key); cls_li.insert(cls_li.end(), cm[k].lane_info, cm[k].lane_info + 32);
+        // where element (unit u, entry e) of a parked tile Gram goes in the symmetric matrix Gs of the expansion:
+        // e < 6 the upper triangle of the unit's own 3x3 block, then 9 entries per partner block column
+        const int nun = h->rowstride / 3, nacc = k1_nacc(h->rowstride), ld = k1_gsld(h->rowstride);
+        for (int u = 0; u < nun; u++)
+          for (int e = 0; e < nacc; e++) {
+            int i = -1, j = -1;
+            if (u < cm[k].nunits) {
+              if (e < 6) { static const int ti[6] = {0, 0, 0, 1, 1, 2}, tj[6] = {0, 1, 2, 1, 2, 2}; i = 3 * u + ti[e]; j = 3 * u + tj[e]; }
+              else { const int d = (e - 6) / 9, r = (e - 6) % 9; if (cm[k].unit_o[d][u] >= 0) { i = 3 * u + r / 3; j = 3 * cm[k].unit_o[d][u] + r % 3; } }
+            }
+            gs_tab.push_back(i < 0 ? -1 : ((i * ld + j) | ((j * ld + i) << 16)));
+          }
+      }
       cm[k].cls = ci;
     }
     h->ncls = (int)classes.size();
@@ -665,14 +674,17 @@ mcc_status build_structure(mcc_handle* h) {
   for (int k = 0; k < ncam; k++) {
     if (!h->cams[k].active) continue;
     const int ncc = cm[k].r_col;   // every local column but the residual; pose columns carry red_col = -1
-    for (int i = 0; i < ncc; i++) {
-      if (cm[k].red_col[i] < 0) continue;
-      for (int j = i; j < ncc; j++) {
-        if (cm[k].red_col[j] < 0) continue;
-        cc.push_back(CcEntry{k, ab_code(cm[k], i, j, h->rowstride), cm[k].red_col[i], cm[k].red_col[j]});
+    // two rounds: the geometry x geometry entries of a camera (extrinsics x extrinsics) come first in its list
+    for (int geo = 1; geo >= 0; geo--)
+      for (int i = 0; i < ncc; i++) {
+        if (cm[k].red_col[i] < 0) continue;
+        for (int j = i; j < ncc; j++) {
+          if (cm[k].red_col[j] < 0 || (int)ab_is_geo(cm[k], i, j) != geo) continue;
+          cc.push_back(CcEntry{k, ab_code(cm[k], i, j, h->rowstride), cm[k].red_col[i], cm[k].red_col[j]});
+          cm[k].n_cc_g += geo;
+        }
+        if (!geo) cc.push_back(CcEntry{k, ab_code(cm[k], i, cm[k].r_col, h->rowstride), cm[k].red_col[i], -1});
       }
-      cc.push_back(CcEntry{k, ab_code(cm[k], i, cm[k].r_col, h->rowstride), cm[k].red_col[i], -1});
-    }
   }
   h->E = (int)cc.size();
   // entry range of every camera in cc[] (entries were pushed camera by camera)
@@ -686,22 +698,27 @@ mcc_status build_structure(mcc_handle* h) {
   // [ext | pose | intr | r] go where (ab_code packs and orders the pair the way the kernel's `entry` expects it).
   //   pose x camera columns  -> H_fc[frame][a * C + reduced column]
   //   camera x camera (+ camera gradient) entries -> index into the camera-camera entry vector
-  //   pose x pose (+ pose gradient) -> entry a * 7 + b of the frame's 6 x 7 block (b == 6: gradient), in this order
+  //   pose x pose (+ pose gradient) -> entry a * 7 + b of the frame's 6 x 7 block (b == 6: gradient)
   std::vector<int2> dist;
   for (int k = 0; k < ncam; k++) {
     CamMeta& m = cm[k];
     m.dist_off = (int)dist.size();
-    for (int a = 0; a < 6; a++)
-      for (int j = 0; j < m.r_col; j++)
-        if (m.red_col[j] >= 0) dist.push_back(make_int2(ab_code(m, j, m.pose_col + a, h->rowstride), a * C + m.red_col[j]));
+    for (int geo = 1; geo >= 0; geo--)
+      for (int a = 0; a < 6; a++)
+        for (int j = 0; j < m.r_col; j++)
+          if (m.red_col[j] >= 0 && (int)ab_is_geo(m, j, m.pose_col + a) == geo) {
+            dist.push_back(make_int2(ab_code(m, j, m.pose_col + a, h->rowstride), a * C + m.red_col[j]));
+            m.n_hfc_g += geo;
+          }
     m.n_hfc = (int)dist.size() - m.dist_off;
     for (int e = cc_e0[k]; e < cc_e0[k + 1]; e++) dist.push_back(make_int2(cc[e].gram_off, e));
     m.n_cc = cc_e0[k + 1] - cc_e0[k];
     m.e0 = cc_e0[k];
-    for (int ent = 0; ent < 42; ent++) {
-      const int a = ent / 7, b2 = ent % 7;
-      dist.push_back(make_int2(ab_code(m, m.pose_col + a, b2 < 6 ? m.pose_col + b2 : m.r_col, h->rowstride), ent));
-    }
+    for (int grad = 0; grad < 2; grad++)       // the 36 pose x pose entries first, then the 6 gradient entries
+      for (int ent = 0; ent < 42; ent++) {
+        const int a = ent / 7, b2 = ent % 7;
+        if ((b2 == 6) == (grad == 1)) dist.push_back(make_int2(ab_code(m, m.pose_col + a, b2 < 6 ? m.pose_col + b2 : m.r_col, h->rowstride), ent));
+      }
   }
 
   // observation offsets, active frames, tiles
@@ -782,6 +799,7 @@ mcc_status build_structure(mcc_handle* h) {
   CU(up(h->d_cc, cc));
   CU(up(h->d_dist, dist));
   CU(up(h->d_cls_li, cls_li));
+  CU(up(h->d_gs_tab, gs_tab));
   CU(h->d_Linv.reserve((size_t)std::max(h->nslots, 1) * 6)); CU(h->d_zf.reserve((size_t)std::max(h->nslots, 1) * 6));
   CU(up(h->d_tiles, tiles));
   CU(up(h->d_gto, gto));
@@ -1094,7 +1112,7 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
   if (h->nslots) {
     K1Args ka;
     ka.nslots = h->nslots; ka.ncam = h->ncam(); ka.C = h->C; ka.maxft = h->maxft; ka.E = h->E; ka.use_loss = use_loss; ka.ncls = h->ncls; ka.gstride = h->gstride;
-    ka.tiles = h->d_tiles.p; ka.gto = h->d_gto.p; ka.cams = h->d_cams.p; ka.cls_lane_info = h->d_cls_li.p; ka.dist = h->d_dist.p;
+    ka.tiles = h->d_tiles.p; ka.gto = h->d_gto.p; ka.cams = h->d_cams.p; ka.cls_lane_info = h->d_cls_li.p; ka.dist = h->d_dist.p; ka.gs_tab = h->d_gs_tab.p;
     ka.camrec = h->d_camrec.p; ka.frot = h->d_frot.p; ka.pose = h->d_pose[which].p;
     ka.oX = h->d_X.p; ka.oY = h->d_Y.p; ka.oZ = h->d_Z.p; ka.oU = h->d_U.p; ka.oV = h->d_V.p; ka.omask = h->d_mask.p;
     ka.Hff = h->d_Hff2[bo].p; ka.gf = h->d_gf2[bo].p; ka.Hfc = h->d_Hfc2[bo].p; ka.cost_f = h->d_cost_f.p; ka.gmax_f = h->d_gmax_f.p; ka.xn2_f = h->d_xn2_f.p;
@@ -1504,7 +1522,7 @@ void mcc_destroy(mcc_handle* h) {
                         &h->d_mcc_f, &h->d_dx2_f, &h->d_xn2c_f, &h->d_cc_part, &h->d_cc_sum, &h->d_Hcc2[0], &h->d_Hcc2[1], &h->d_gc2[0], &h->d_gc2[1], &h->d_scale_c, &h->d_scale_f, &h->d_S_part,
                         &h->d_S_sum, &h->d_M, &h->d_yc, &h->d_ysc, &h->d_scal};
   for (auto* b : dd) b->release();
-  h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_tab.release(); h->d_col_param.release(); h->d_dist.release(); h->d_cls_li.release();
+  h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_tab.release(); h->d_col_param.release(); h->d_dist.release(); h->d_cls_li.release(); h->d_gs_tab.release();
   h->d_cams.release(); h->d_cc.release(); h->d_Linv.release(); h->d_zf.release();
   h->world.release(); h->image.release();
   if (h->h_scal) cudaFreeHost(h->h_scal);
