@@ -292,7 +292,9 @@ struct mcc_handle {
   DBuf<int2> d_dist;                   // hand-out lists of the Jacobian pass (per camera: pose x camera, camera x camera, pose x pose)
   DBuf<uint4> d_cls_li;                // lane records per camera class
   DBuf<double> d_Linv, d_zf;
-  int ncls = 0, maxft = 1, k1_grid = 1;
+  int ncls = 0, maxft = 1, k1_grid = 1, k1_fs = 0, cc_rows = 1;   // Jacobian pass: grid, statically dealt frames, rows of cc_part
+  unsigned int* d_ticket = nullptr;    // [0] frame counter of the Jacobian pass, [1..] entry-block counters of k_reduce_misc
+  DBuf<double> d_cc_part2;
   DBuf<CamMeta> d_cams;
   DBuf<CcEntry> d_cc;
   DBuf<double> d_camp[2], d_pose[2];   // current / candidate
@@ -421,6 +423,8 @@ mcc_status ensure_device(mcc_handle* h) {
   if (!h->h_scal) CU(cudaHostAlloc((void**)&h->h_scal, 33 * sizeof(double), cudaHostAllocDefault));
   if (!h->d_state) {
     CU(cudaMalloc((void**)&h->d_state, sizeof(LmState)));
+    CU(cudaMalloc((void**)&h->d_ticket, 64 * sizeof(unsigned int)));
+    CU(cudaMemset(h->d_ticket, 0, 64 * sizeof(unsigned int)));   // both kernels leave their counters at zero
     CU(cudaHostAlloc((void**)&h->h_rec, 2 * LM_REC * sizeof(double), cudaHostAllocMapped));   // decide_body writes the records straight to the host
     CU(cudaHostGetDevicePointer((void**)&h->d_rec, h->h_rec, 0));
     for (int i = 0; i < 2; i++) CU(cudaEventCreateWithFlags(&h->ev_rec[i], cudaEventDisableTiming));
@@ -785,6 +789,13 @@ mcc_status build_structure(mcc_handle* h) {
     if (h->rowstride == 15) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_frame_normal<15>, K1_WARPS * 32, smem));
     else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_frame_normal<21>, K1_WARPS * 32, smem));
     h->k1_grid = std::max(1, std::min(std::max(h->nslots, 1), std::max(occ, 1) * sms));
+    // half of the frames in whole static rounds, the rest (and the remainder) from the counter: measured on c4, static
+    // fraction 1 / 0.75 / 0.5 / 0.25 / 0: Jacobian pass 0.757 / 0.727 / 0.720 / 0.712 / 0.706 ms, but the row reduction grows
+    // with the number of per-frame rows (whole step 6.03 / 5.89 / 5.85 / 5.86 / 5.89 ms)
+    double frac = 0.5;
+    if (const char* e = std::getenv("MCC_K1_STATIC_FRAC")) frac = std::min(1.0, std::max(0.0, std::atof(e)));
+    h->k1_fs = (int)(frac * h->nslots / h->k1_grid) * h->k1_grid;
+    h->cc_rows = h->k1_grid + (h->nslots - h->k1_fs);
   }
 
   // upload structure
@@ -812,7 +823,8 @@ mcc_status build_structure(mcc_handle* h) {
   CU(h->d_Lf.reserve(ns * 36));
   CU(h->d_cost_f.reserve(ns)); CU(h->d_gmax_f.reserve(ns)); CU(h->d_xn2_f.reserve(ns)); CU(h->d_newcost_f.reserve(ns));
   CU(h->d_mcc_f.reserve(ns)); CU(h->d_dx2_f.reserve(ns)); CU(h->d_xn2c_f.reserve(ns));
-  CU(h->d_cc_part.reserve((size_t)h->k1_grid * std::max(h->E, 1))); CU(h->d_cc_sum.reserve((size_t)h->E + COMM_SCAL + 2 * 64));
+  CU(h->d_cc_part.reserve((size_t)h->cc_rows * std::max(h->E, 1))); CU(h->d_cc_part2.reserve((size_t)CCR_RS * std::max(h->E, 1)));
+  if ((h->E + CCR_E - 1) / CCR_E > 63) return fail(h, MCC_ERR_TOO_LARGE, "too many camera-camera entries (%d)", h->E); CU(h->d_cc_sum.reserve((size_t)h->E + COMM_SCAL + 2 * 64));
   for (int b = 0; b < 2; b++) { CU(h->d_Hcc2[b].reserve((size_t)std::max(C, 1) * std::max(C, 1))); CU(h->d_gc2[b].reserve(std::max(C, 1))); }
   CU(h->d_scale_c.reserve(std::max(C, 1))); CU(h->d_scale_f.reserve(ns * 6));
   CU(h->d_S_part.reserve((size_t)h->sy_gx * h->npairs * SY_T * SY_T)); CU(h->d_S_sum.reserve((size_t)h->npairs * SY_T * SY_T));
@@ -1116,7 +1128,7 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
     ka.camrec = h->d_camrec.p; ka.frot = h->d_frot.p; ka.pose = h->d_pose[which].p;
     ka.oX = h->d_X.p; ka.oY = h->d_Y.p; ka.oZ = h->d_Z.p; ka.oU = h->d_U.p; ka.oV = h->d_V.p; ka.omask = h->d_mask.p;
     ka.Hff = h->d_Hff2[bo].p; ka.gf = h->d_gf2[bo].p; ka.Hfc = h->d_Hfc2[bo].p; ka.cost_f = h->d_cost_f.p; ka.gmax_f = h->d_gmax_f.p; ka.xn2_f = h->d_xn2_f.p;
-    ka.cc_part = h->d_cc_part.p; ka.st = h->st_cur;
+    ka.cc_part = h->d_cc_part.p; ka.st = h->st_cur; ka.fs = h->k1_fs; ka.ticket = h->d_ticket;
     const size_t smem = k1_smem_bytes(h->rowstride, h->ncam(), h->maxft);
     {
       KScope ks(h, KC_SETUP);
@@ -1137,8 +1149,9 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
   {
     KScope ks(h, KC_REDUCE);
     // camera-camera entries: one partial row per CTA of the Jacobian pass (no rows at all on a rank without frames)
-    const int ncc = (h->E + CCR_E - 1) / CCR_E;
-    k_reduce_misc<<<ncc + 3 + nextra, 1024, 0, h->stream>>>(ncc, h->E, h->nslots ? h->k1_grid : 0, h->d_cc_part.p, cc_sum_buf(h), jobs, h->nslots, h->d_scal.p, h->st_cur);
+    const int ncc = (h->E + CCR_E - 1) / CCR_E * CCR_RS;
+    k_reduce_misc<<<ncc + 3 + nextra, 1024, 0, h->stream>>>(ncc, h->E, h->nslots ? h->cc_rows : 0, h->d_cc_part.p, h->d_cc_part2.p, cc_sum_buf(h), h->d_ticket + 1, jobs,
+                                                            h->nslots, h->d_scal.p, h->st_cur);
   }
   CU(cudaGetLastError());
   if (multi) {
@@ -1519,7 +1532,7 @@ void mcc_destroy(mcc_handle* h) {
   if (h->comm && nccl().CommDestroy) nccl().CommDestroy(h->comm);
   DBuf<double>* dd[] = {&h->d_aos_w, &h->d_aos_i, &h->d_X, &h->d_Y, &h->d_Z, &h->d_U, &h->d_V, &h->d_res, &h->d_camp[0], &h->d_camp[1], &h->d_pose[0], &h->d_pose[1],
                         &h->d_setup, &h->d_frot, &h->d_camrec, &h->d_tile_s, &h->d_Hff2[0], &h->d_Hff2[1], &h->d_gf2[0], &h->d_gf2[1], &h->d_Hfc2[0], &h->d_Hfc2[1], &h->d_Lf, &h->d_cost_f, &h->d_gmax_f, &h->d_xn2_f, &h->d_newcost_f,
-                        &h->d_mcc_f, &h->d_dx2_f, &h->d_xn2c_f, &h->d_cc_part, &h->d_cc_sum, &h->d_Hcc2[0], &h->d_Hcc2[1], &h->d_gc2[0], &h->d_gc2[1], &h->d_scale_c, &h->d_scale_f, &h->d_S_part,
+                        &h->d_mcc_f, &h->d_dx2_f, &h->d_xn2c_f, &h->d_cc_part, &h->d_cc_part2, &h->d_cc_sum, &h->d_Hcc2[0], &h->d_Hcc2[1], &h->d_gc2[0], &h->d_gc2[1], &h->d_scale_c, &h->d_scale_f, &h->d_S_part,
                         &h->d_S_sum, &h->d_M, &h->d_yc, &h->d_ysc, &h->d_scal};
   for (auto* b : dd) b->release();
   h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_tab.release(); h->d_col_param.release(); h->d_dist.release(); h->d_cls_li.release(); h->d_gs_tab.release();
@@ -1527,7 +1540,7 @@ void mcc_destroy(mcc_handle* h) {
   h->world.release(); h->image.release();
   if (h->h_scal) cudaFreeHost(h->h_scal);
   drop_iteration_graphs(h);
-  if (h->d_state) { cudaFree(h->d_state); cudaFreeHost(h->h_rec); for (int i = 0; i < 2; i++) cudaEventDestroy(h->ev_rec[i]); }
+  if (h->d_state) { cudaFree(h->d_state); cudaFree(h->d_ticket); cudaFreeHost(h->h_rec); for (int i = 0; i < 2; i++) cudaEventDestroy(h->ev_rec[i]); }
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   for (KPending& pe : h->ev_pending) { cudaEventDestroy(pe.a); cudaEventDestroy(pe.b); }
   if (h->tm_a) { cudaEventDestroy(h->tm_a); cudaEventDestroy(h->tm_b); }
