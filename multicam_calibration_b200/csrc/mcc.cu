@@ -379,6 +379,15 @@ void materialize_mask(mcc_handle* h) {
   if (h->mask.size() != h->nobs) h->mask.resize(h->nobs, 1);
 }
 
+// Launch of a kernel of the LM iteration.  (Programmatic dependent launch between them -- cudaLaunchAttributeProgrammaticStreamSerialization
+// plus griddepcontrol.wait / launch_dependents at the top of every kernel -- was measured: 6.00 instead of 5.85 ms per step; dropped.)
+template <typename... KArgs, typename... Args>
+cudaError_t launch_k(mcc_handle* h, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = h->stream;
+  return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+
 struct KScope {
   mcc_handle* h;
   KPending p;
@@ -1098,7 +1107,7 @@ mcc_status peer_allreduce(mcc_handle* h, int ex, double* p, size_t n) {
   const unsigned int seq32 = (unsigned int)(seq % 0xffffffffull) + 1u;
   {
     KScope ks(h, KC_EXCHANGE);   // includes the wait for the slowest rank
-    k_peer_allreduce<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->pw, p, (int)n, off, seq32, ex, base, slot_n, fail_ptr(h), h->peer_timeout_cycles, h->st_cur);
+    CU(launch_k(h, k_peer_allreduce, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, h->pw, p, (int)n, off, seq32, ex, base, slot_n, fail_ptr(h), h->peer_timeout_cycles, h->st_cur));
   }
   CU(cudaGetLastError());
   return MCC_OK;
@@ -1116,7 +1125,7 @@ mcc_status allreduce(mcc_handle* h, double* p, size_t n, int op) {
 // Several ranks: the camera-camera entries and every scalar of the iteration travel in ONE all-reduce (sum) over
 // d_cc_sum = [entries E | 6 scalars | gradient max per rank | failure flag per rank]; k_scatter_cc unpacks it.
 // extra: further per-frame arrays to reduce in the same launch (launch_step's scalars of a speculative step).
-mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const ReduceJob* extra = nullptr, int nextra = 0) {
+mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const ReduceJob* extra = nullptr, int nextra = 0, bool rot_ready = false) {
   const bool multi = h->nranks > 1;
   double* tail = cc_sum_buf(h) + h->E;
   // the per-rank slots of the other ranks have to be zero; on one rank every entry is written (k_reduce_misc)
@@ -1130,14 +1139,14 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
     ka.Hff = h->d_Hff2[bo].p; ka.gf = h->d_gf2[bo].p; ka.Hfc = h->d_Hfc2[bo].p; ka.cost_f = h->d_cost_f.p; ka.gmax_f = h->d_gmax_f.p; ka.xn2_f = h->d_xn2_f.p;
     ka.cc_part = h->d_cc_part.p; ka.st = h->st_cur; ka.fs = h->k1_fs; ka.ticket = h->d_ticket;
     const size_t smem = k1_smem_bytes(h->rowstride, h->ncam(), h->maxft);
-    {
+    if (!rot_ready) {     // inside an LM iteration k_solve_cam and k_backsub have already made the records of the candidate
       KScope ks(h, KC_SETUP);
-      k_rot_setup<<<(h->nslots + h->ncam() + 127) / 128, 128, 0, h->stream>>>(h->nslots, h->ncam(), h->d_cams.p, h->d_camp[which].p, h->d_pose[which].p, h->d_frot.p,
-                                                                              h->d_camrec.p, h->st_cur);
+      CU(launch_k(h, k_rot_setup, dim3((h->nslots + h->ncam() + 127) / 128), dim3(128), 0, h->nslots, h->ncam(), h->d_cams.p, h->d_camp[which].p, h->d_pose[which].p, h->d_frot.p,
+                                                                              h->d_camrec.p, h->st_cur));
     }
     KScope ks(h, KC_TILE_NORMAL);
-    if (h->rowstride == 15) k_frame_normal<15><<<h->k1_grid, K1_WARPS * 32, smem, h->stream>>>(ka);
-    else k_frame_normal<21><<<h->k1_grid, K1_WARPS * 32, smem, h->stream>>>(ka);
+    if (h->rowstride == 15) CU(launch_k(h, k_frame_normal<15>, dim3(h->k1_grid), dim3(K1_WARPS * 32), smem, ka));
+    else CU(launch_k(h, k_frame_normal<21>, dim3(h->k1_grid), dim3(K1_WARPS * 32), smem, ka));
   }
   CU(cudaGetLastError());
   ReduceJobs jobs;
@@ -1150,8 +1159,8 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
     KScope ks(h, KC_REDUCE);
     // camera-camera entries: one partial row per CTA of the Jacobian pass (no rows at all on a rank without frames)
     const int ncc = (h->E + CCR_E - 1) / CCR_E * CCR_RS;
-    k_reduce_misc<<<ncc + 3 + nextra, 1024, 0, h->stream>>>(ncc, h->E, h->nslots ? h->cc_rows : 0, h->d_cc_part.p, h->d_cc_part2.p, cc_sum_buf(h), h->d_ticket + 1, jobs,
-                                                            h->nslots, h->d_scal.p, h->st_cur);
+    CU(launch_k(h, k_reduce_misc, dim3(ncc + 3 + nextra), dim3(1024), 0, ncc, h->E, h->nslots ? h->cc_rows : 0, h->d_cc_part.p, h->d_cc_part2.p, cc_sum_buf(h), h->d_ticket + 1, jobs,
+                                                            h->nslots, h->d_scal.p, h->st_cur));
   }
   CU(cudaGetLastError());
   if (multi) {
@@ -1161,8 +1170,8 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
   }
   {
     KScope ks(h, KC_REDUCE);
-    k_scatter_cc<<<1, 1024, 0, h->stream>>>(h->C, h->E, h->d_cc.p, cc_sum_buf(h), h->d_col_param.p, h->d_camp[which].p, h->d_Hcc2[bo].p, h->d_gc2[bo].p, h->d_scal.p + 8,
-                                             h->nranks, h->d_scal.p, fail_ptr(h), h->decide, h->st_cur);
+    CU(launch_k(h, k_scatter_cc, dim3(1), dim3(1024), 0, h->C, h->E, h->d_cc.p, cc_sum_buf(h), h->d_col_param.p, h->d_camp[which].p, h->d_Hcc2[bo].p, h->d_gc2[bo].p, h->d_scal.p + 8,
+                                             h->nranks, h->d_scal.p, fail_ptr(h), h->decide, h->st_cur));
   }
   CU(cudaGetLastError());
   return MCC_OK;
@@ -1199,8 +1208,8 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
   {
     if (h->nslots) {
       KScope ks(h, KC_SCHUR);
-      k_frame_chol<<<(h->nslots + 127) / 128, 128, 0, h->stream>>>(h->nslots, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hff2[h->blk].p, h->d_gf2[h->blk].p, h->d_scale_f.p,
-                                                                    h->d_Lf.p, h->d_Linv.p, h->d_zf.p, fail_ptr(h), h->st_cur);
+      CU(launch_k(h, k_frame_chol, dim3((h->nslots + 127) / 128), dim3(128), 0, h->nslots, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hff2[h->blk].p, h->d_gf2[h->blk].p, h->d_scale_f.p,
+                                                                    h->d_Lf.p, h->d_Linv.p, h->d_zf.p, fail_ptr(h), h->st_cur));
     }
     CU(cudaGetLastError());
     auto schur_smem = [&](int fb, bool pf) {
@@ -1212,8 +1221,8 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     {
       KScope ks(h, KC_SCHUR);
 #define MCC_LAUNCH_SCHUR(PF, FB)                                                                                                                   \
-      k_schur_syrk<PF, FB><<<grid, SY_THREADS, schur_smem(FB, PF), h->stream>>>(h->nslots, C, h->LD, h->npairs, h->d_Hfc2[h->blk].p, h->d_scale_f.p,     \
-                                                                                h->d_scale_c.p, h->d_Lf.p, h->d_Linv.p, h->d_zf.p, h->d_S_part.p, h->st_cur)
+      CU((launch_k(h, k_schur_syrk<PF, FB>, grid, dim3(SY_THREADS), schur_smem(FB, PF), h->nslots, C, h->LD, h->npairs, h->d_Hfc2[h->blk].p, h->d_scale_f.p,     \
+                                                                                h->d_scale_c.p, h->d_Lf.p, h->d_Linv.p, h->d_zf.p, h->d_S_part.p, h->st_cur)))
       // prefetch variants keep two CTAs per SM (<= 112 KB each): 8 frames per batch, else 4; wider systems read Hfc from global memory
       if (schur_smem(8, true) <= 112 * 1024) MCC_LAUNCH_SCHUR(true, 8);
       else if (schur_smem(4, true) <= 112 * 1024) MCC_LAUNCH_SCHUR(true, 4);
@@ -1224,7 +1233,7 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     const int n = h->npairs * SY_T * SY_T;
     {
       KScope ks(h, KC_REDUCE);
-      k_reduce_rows<<<(n + RR_E - 1) / RR_E, RR_E * RR_S, 0, h->stream>>>(h->sy_gx, n, h->d_S_part.p, S_sum_buf(h), h->st_cur);
+      CU(launch_k(h, k_reduce_rows, dim3((n + RR_E - 1) / RR_E), dim3(RR_E * RR_S), 0, h->sy_gx, n, h->d_S_part.p, S_sum_buf(h), h->st_cur));
     }
     CU(cudaGetLastError());
     if (h->peer_on) ST(peer_allreduce(h, 0, S_sum_buf(h), n));
@@ -1236,21 +1245,21 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     {
       KScope ks(h, KC_SOLVE);
       if (packed)
-        k_solve_cam<true><<<1, CH_THREADS, need, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc2[h->blk].p, h->d_gc2[h->blk].p, S_sum_buf(h),
+        CU(launch_k(h, k_solve_cam<true>, dim3(1), dim3(CH_THREADS), need, C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc2[h->blk].p, h->d_gc2[h->blk].p, S_sum_buf(h),
                                                               h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
-                                                              h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, fail_ptr(h), h->st_cur);
+                                                              h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, fail_ptr(h), h->d_cams.p, h->ncam(), h->d_camrec.p, h->st_cur));
       else
-        k_solve_cam<false><<<1, CH_THREADS, 0, h->stream>>>(C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc2[h->blk].p, h->d_gc2[h->blk].p, S_sum_buf(h),
+        CU(launch_k(h, k_solve_cam<false>, dim3(1), dim3(CH_THREADS), 0, C, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hcc2[h->blk].p, h->d_gc2[h->blk].p, S_sum_buf(h),
                                                             h->d_scale_c.p, h->d_col_param.p, h->C_full, h->d_camp[cur].p, h->d_camp[cand].p, h->d_yc.p,
-                                                            h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, fail_ptr(h), h->st_cur);
+                                                            h->d_ysc.p, h->d_M.p, h->d_scal.p + 10, fail_ptr(h), h->d_cams.p, h->ncam(), h->d_camrec.p, h->st_cur));
     }
     CU(cudaGetLastError());
   }
   if (h->nslots) {
     {
       KScope ks(h, KC_BACKSUB);
-      k_backsub<<<(h->nslots + 3) / 4, 128, 0, h->stream>>>(h->nslots, C, h->d_Hff2[h->blk].p, h->d_gf2[h->blk].p, h->d_Hfc2[h->blk].p, h->d_Lf.p, h->d_scale_f.p, h->d_ysc.p,
-                                                         h->d_pose[cur].p, h->d_pose[cand].p, h->d_mcc_f.p, h->d_dx2_f.p, h->d_xn2c_f.p, fail_ptr(h), h->st_cur);
+      CU(launch_k(h, k_backsub, dim3((h->nslots + 3) / 4), dim3(128), 0, h->nslots, C, h->d_Hff2[h->blk].p, h->d_gf2[h->blk].p, h->d_Hfc2[h->blk].p, h->d_Lf.p, h->d_scale_f.p, h->d_ysc.p,
+                                                         h->d_pose[cur].p, h->d_pose[cand].p, h->d_mcc_f.p, h->d_dx2_f.p, h->d_xn2c_f.p, fail_ptr(h), h->d_frot.p, h->st_cur));
     }
     CU(cudaGetLastError());
   }
@@ -1266,7 +1275,7 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     extra[1] = ReduceJob{h->d_dx2_f.p, 0, multi ? tail + 4 : h->d_scal.p + 5};
     extra[2] = ReduceJob{h->d_xn2c_f.p, 0, multi ? tail + 5 : h->d_scal.p + 6};
     extra[3] = ReduceJob{reinterpret_cast<const double*>(fail_ptr(h)), 2, tail + COMM_SCAL + h->nranks + h->rank};
-    ST(launch_jacobian(h, o.use_loss, cand, 1 - h->blk, extra, multi ? 4 : 3));   // cost, |x|^2, gradient norm -> d_scal[0..2], [8..9]
+    ST(launch_jacobian(h, o.use_loss, cand, 1 - h->blk, extra, multi ? 4 : 3, true));   // cost, |x|^2, gradient norm -> d_scal[0..2], [8..9]
     return MCC_OK;
   }
   ST(launch_cost(h, cand, o.use_loss, h->d_newcost_f.p, nullptr));

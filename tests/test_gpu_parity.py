@@ -409,6 +409,21 @@ def test_bench_configs_match_oracle(built, config, nframes):
     cal.close()
 
 
+def test_rejected_steps_match_oracle(built):
+    """a solve with five rejected steps in a row (tests/fixtures_util.py): radius halving, the cost-only candidate pass and the
+    return to speculative iterations must follow the oracle row by row"""
+    from multicam_calibration_b200 import capi
+    import oracle
+    from fixtures_util import rejected_steps_rig
+    rig, mrd = rejected_steps_rig()
+    cal, orc = _pair(rig)
+    og, oo = capi.default_options(), oracle.default_options()
+    og.min_relative_decrease = oo.min_relative_decrease = mrd
+    sg, so = _check_solve(cal, orc, og, oo)
+    assert so.num_unsuccessful == 5 and sg.num_unsuccessful == 5
+    cal.close()
+
+
 def test_queued_iterations_match_synchronous_path(small_rig, kat_rigs, monkeypatch):
     """solve() queues iterations ahead of their accept / reject decision (decided on the device, replayed as CUDA
     graphs); MCC_PIPELINE=0 / MCC_GRAPHS=0 take the ordinary synchronous path.  Same arithmetic, same decisions:

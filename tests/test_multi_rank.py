@@ -47,7 +47,7 @@ def _gpu_count():
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("p2p", ["1", "0"])
-@pytest.mark.parametrize("case", ["small", "equidistant", "c4", "empty"])
+@pytest.mark.parametrize("case", ["small", "rejected", "c4", "empty"])
 def test_sharded_solve(built, case, p2p):
     """all GPUs of the box (2, 4 or 8 ranks), frames sharded by observation count, against the oracle's solve of the
     whole rig: the per-iteration exchanges go through the peer-memory all-reduce (MCC_P2P=1, the default on one node) or
@@ -56,5 +56,5 @@ def test_sharded_solve(built, case, p2p):
     if n < 2:
         pytest.skip("needs >= 2 GPUs (run under gpurun --gpus 2)")
     n = 8 if n >= 8 else (4 if n >= 4 else 2)
-    out = _launch(["nccl-solve", case], n, 29620 + 2 * ["small", "equidistant", "c4", "empty"].index(case) + int(p2p), {"MCC_P2P": p2p})
+    out = _launch(["nccl-solve", case], n, 29620 + 2 * ["small", "rejected", "c4", "empty"].index(case) + int(p2p), {"MCC_P2P": p2p})
     print(out[-400:])
