@@ -312,7 +312,8 @@ struct mcc_handle {
   PeerWin pw{};
   uint4* peer_own = nullptr;            // this rank's window (cudaMalloc)
   size_t peer_nS = 0, peer_nC = 0;      // slot sizes the window was laid out for
-  unsigned long long peer_seq[2] = {0, 0};
+  unsigned long long peer_seq[3] = {0, 0, 0};
+  DBuf<double> d_small;                 // [4 scalars | failure flag per rank] of a non-speculative step (several ranks)
   bool peer_on = false, peer_failed = false;
   long long peer_timeout_cycles = 0;    // k_peer_allreduce gives up after this many SM clocks (MCC_PEER_TIMEOUT_S, default 60 s)
   // iterations queued ahead of their accept / reject decision (solve(): pipelined section)
@@ -445,7 +446,7 @@ mcc_status ensure_device(mcc_handle* h) {
     CU((cudaFuncSetAttribute(k_schur_syrk<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)));
     CU((cudaFuncSetAttribute(k_schur_syrk<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)));
     CU((cudaFuncSetAttribute(k_schur_syrk<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)));
-    CU(cudaFuncSetAttribute(k_solve_cam<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 196 * 1024));
+    CU(cudaFuncSetAttribute(k_solve_cam<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 184 * 1024));
     h->attrs_set = true;
   }
   return MCC_OK;
@@ -838,7 +839,7 @@ mcc_status build_structure(mcc_handle* h) {
   CU(h->d_scale_c.reserve(std::max(C, 1))); CU(h->d_scale_f.reserve(ns * 6));
   CU(h->d_S_part.reserve((size_t)h->sy_gx * h->npairs * SY_T * SY_T)); CU(h->d_S_sum.reserve((size_t)h->npairs * SY_T * SY_T));
   CU(h->d_M.reserve((size_t)(C + 1) * std::max(C, 1))); CU(h->d_yc.reserve(std::max(C, 1))); CU(h->d_ysc.reserve(std::max(C, 1)));
-  CU(h->d_scal.reserve(40));   // 32 scalars + the failure flags (an int at [32]) so that one copy brings both back
+  CU(h->d_scal.reserve(40)); CU(h->d_small.reserve(4 + 64));   // 32 scalars + the failure flags (an int at [32]) so that one copy brings both back
   for (int i = 0; i < 2; i++) { CU(h->d_camp[i].reserve(std::max(h->C_full, 1))); CU(h->d_pose[i].reserve(ns * 6)); }
   CU(cudaStreamSynchronize(h->stream));   // the staging vectors above die with this scope
   h->structure_dirty = false;
@@ -1022,7 +1023,7 @@ mcc_status ensure_peer_window(mcc_handle* h) {
   free_peer_window(h);
   h->peer_failed = false;
   const int R = h->nranks;
-  const size_t cells = 2 * (size_t)R * (nS + nC);   // 2 parities x R slots per exchange, 16 bytes per value
+  const size_t cells = 2 * (size_t)R * (nS + nC + PEER_SMALL);   // 2 parities x R slots per exchange class, 16 bytes per value
   int bad = 0;
   if (cudaMalloc((void**)&h->peer_own, cells * sizeof(uint4)) != cudaSuccess) { h->peer_own = nullptr; bad = 1; }
   cudaIpcMemHandle_t mine;
@@ -1090,24 +1091,28 @@ mcc_status ensure_peer_window(mcc_handle* h) {
     if (const char* e = std::getenv("MCC_PEER_TIMEOUT_S")) { const double v = std::atof(e); if (v > 0.0) secs = v; }
     h->peer_timeout_cycles = (long long)(secs * 2.0e9);
   }
-  h->peer_nS = nS; h->peer_nC = nC; h->peer_seq[0] = h->peer_seq[1] = 0; h->peer_on = true;
+  h->peer_nS = nS; h->peer_nC = nC; h->peer_seq[0] = h->peer_seq[1] = h->peer_seq[2] = 0; h->peer_on = true;
   return MCC_OK;
 }
 
-// exchange 0: Schur tile pairs (n = peer_nS), exchange 1: camera-camera entries + scalars (n <= peer_nC)
+// exchange 0: Schur tile pairs (n = peer_nS), exchange 1: camera-camera entries + scalars (n <= peer_nC).
+// The descriptor of the next exchange of class ex; queued iterations (st_cur set) take the sequence number from the device
+// state, which the host mirrors from the decision records.
+PeerEx peer_ex(mcc_handle* h, int ex) {
+  PeerEx px;
+  px.pw = h->pw; px.ex = ex;
+  px.slot_n = ex == 0 ? h->peer_nS : (ex == 1 ? h->peer_nC : (size_t)PEER_SMALL);
+  px.ex_base = ex == 0 ? 0 : 2 * (size_t)h->nranks * (ex == 1 ? h->peer_nS : h->peer_nS + h->peer_nC);
+  px.seq = (h->st_cur && ex < 2) ? h->peer_seq[ex] + 1 : ++h->peer_seq[ex];
+  px.timeout = h->peer_timeout_cycles;
+  return px;
+}
 mcc_status peer_allreduce(mcc_handle* h, int ex, double* p, size_t n) {
-  const int R = h->nranks;
-  // queued iterations (st_cur set): the device state carries the sequence numbers, the host mirrors them from the records
-  const unsigned long long seq = h->st_cur ? h->peer_seq[ex] + 1 : ++h->peer_seq[ex];
-  const size_t slot_n = ex == 0 ? h->peer_nS : h->peer_nC;
-  if (n > slot_n) return fail(h, MCC_ERR_NCCL, "peer window laid out for another size");
-  const size_t base = ex == 0 ? 0 : 2 * (size_t)R * h->peer_nS;
-  const size_t off = base + (seq & 1) * (size_t)R * slot_n;
-  // the sequence number in the cells is 32 bits and never 0 (0 = a fresh window)
-  const unsigned int seq32 = (unsigned int)(seq % 0xffffffffull) + 1u;
+  const PeerEx px = peer_ex(h, ex);
+  if (n > px.slot_n) return fail(h, MCC_ERR_NCCL, "peer window laid out for another size");
   {
     KScope ks(h, KC_EXCHANGE);   // includes the wait for the slowest rank
-    CU(launch_k(h, k_peer_allreduce, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, h->pw, p, (int)n, off, seq32, ex, base, slot_n, fail_ptr(h), h->peer_timeout_cycles, h->st_cur));
+    CU(launch_k(h, k_peer_allreduce, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, px, p, (int)n, fail_ptr(h), h->st_cur));
   }
   CU(cudaGetLastError());
   return MCC_OK;
@@ -1116,8 +1121,15 @@ mcc_status peer_allreduce(mcc_handle* h, int ex, double* p, size_t n) {
 mcc_status allreduce(mcc_handle* h, double* p, size_t n, int op) {
   if (h->nranks <= 1 || n == 0) return MCC_OK;
   KScope ks(h, KC_EXCHANGE);
+  if (!h->comm) return fail(h, MCC_ERR_NCCL, "no NCCL communicator and no peer windows between the devices");
   NC(nccl().AllReduce(p, p, n, ncclFloat64_, op, h->comm, h->stream));
   return MCC_OK;
+}
+// sum over the ranks of a few doubles (<= PEER_SMALL), outside queued iterations: peer windows if there are any, else NCCL
+mcc_status allreduce_small(mcc_handle* h, double* p, size_t n) {
+  if (h->nranks <= 1 || n == 0) return MCC_OK;
+  if (h->peer_on) return peer_allreduce(h, 2, p, n);
+  return allreduce(h, p, n, ncclSum_);
 }
 
 // K1 at the current parameters: blocks, cost, gradient norm, |x|^2 -> d_scal[0..2], [8..9]
@@ -1128,8 +1140,6 @@ mcc_status allreduce(mcc_handle* h, double* p, size_t n, int op) {
 mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const ReduceJob* extra = nullptr, int nextra = 0, bool rot_ready = false) {
   const bool multi = h->nranks > 1;
   double* tail = cc_sum_buf(h) + h->E;
-  // the per-rank slots of the other ranks have to be zero; on one rank every entry is written (k_reduce_misc)
-  if (multi) CU(cudaMemsetAsync(cc_sum_buf(h), 0, ((size_t)h->E + COMM_SCAL + 2 * 64) * sizeof(double), h->stream));
   if (h->nslots) {
     K1Args ka;
     ka.nslots = h->nslots; ka.ncam = h->ncam(); ka.C = h->C; ka.maxft = h->maxft; ka.E = h->E; ka.use_loss = use_loss; ka.ncls = h->ncls; ka.gstride = h->gstride;
@@ -1149,29 +1159,38 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
     else CU(launch_k(h, k_frame_normal<21>, dim3(h->k1_grid), dim3(K1_WARPS * 32), smem, ka));
   }
   CU(cudaGetLastError());
-  ReduceJobs jobs;
-  std::memset(&jobs, 0, sizeof(jobs));
-  jobs.j[0] = ReduceJob{h->d_cost_f.p, 0, multi ? tail + 0 : nullptr};
-  jobs.j[1] = ReduceJob{h->d_xn2_f.p, 0, multi ? tail + 1 : nullptr};
-  jobs.j[2] = ReduceJob{h->d_gmax_f.p, 1, multi ? tail + COMM_SCAL + h->rank : nullptr};
-  for (int i = 0; i < nextra && i < 5; i++) jobs.j[3 + i] = extra[i];
+  // the tail of the pass in one launch (k_reduce_misc): row and array reductions, with several ranks the exchange of the
+  // camera-camera entries and scalars through the peer windows, dense H_cc / g_c and the decision of a queued iteration.
+  // Without peer windows the exchange is an NCCL all-reduce between two launches.
+  static const bool fused_env = !(std::getenv("MCC_FUSED_TAIL") && std::getenv("MCC_FUSED_TAIL")[0] == '0');
+  const bool fused = fused_env && (!multi || h->peer_on);
+  if (multi && !fused) CU(cudaMemsetAsync(cc_sum_buf(h), 0, ((size_t)h->E + COMM_SCAL + 2 * 64) * sizeof(double), h->stream));   // the other ranks' slots
+  TailArgs ta;
+  std::memset(&ta, 0, sizeof(ta));
+  ta.jobs.j[0] = ReduceJob{h->d_cost_f.p, 0, multi ? tail + 0 : nullptr};
+  ta.jobs.j[1] = ReduceJob{h->d_xn2_f.p, 0, multi ? tail + 1 : nullptr};
+  ta.jobs.j[2] = ReduceJob{h->d_gmax_f.p, 1, multi ? tail + COMM_SCAL + h->rank : nullptr};
+  for (int i = 0; i < nextra && i < 5; i++) ta.jobs.j[3 + i] = extra[i];
+  ta.ncc = (h->E + CCR_E - 1) / CCR_E * CCR_RS;
+  ta.E = h->E; ta.nrows = h->nslots ? h->cc_rows : 0; ta.n = h->nslots; ta.tail = fused; ta.has_flag_job = nextra > 0;
+  ta.part = h->d_cc_part.p; ta.part2 = h->d_cc_part2.p; ta.cc_sum = cc_sum_buf(h); ta.counters = h->d_ticket + 1; ta.out = h->d_scal.p;
+  ta.rank = h->rank;
+  ta.px.pw.nranks = 1;
+  if (multi && fused) {
+    if ((size_t)h->E + COMM_SCAL + 2 * h->nranks > h->peer_nC) return fail(h, MCC_ERR_NCCL, "peer window laid out for another size");
+    ta.px = peer_ex(h, 1);
+  }
+  ScatterArgs& sc = ta.sc;
+  sc.C = h->C; sc.E = h->E; sc.nranks = h->nranks; sc.cc = h->d_cc.p; sc.cc_sum = cc_sum_buf(h); sc.col_param = h->d_col_param.p; sc.camp = h->d_camp[which].p;
+  sc.Hcc = h->d_Hcc2[bo].p; sc.gc = h->d_gc2[bo].p; sc.scal = h->d_scal.p + 8; sc.scal_all = h->d_scal.p; sc.fail = fail_ptr(h); sc.da = h->decide;
   {
     KScope ks(h, KC_REDUCE);
-    // camera-camera entries: one partial row per CTA of the Jacobian pass (no rows at all on a rank without frames)
-    const int ncc = (h->E + CCR_E - 1) / CCR_E * CCR_RS;
-    CU(launch_k(h, k_reduce_misc, dim3(ncc + 3 + nextra), dim3(1024), 0, ncc, h->E, h->nslots ? h->cc_rows : 0, h->d_cc_part.p, h->d_cc_part2.p, cc_sum_buf(h), h->d_ticket + 1, jobs,
-                                                            h->nslots, h->d_scal.p, h->st_cur));
+    CU(launch_k(h, k_reduce_misc, dim3(ta.ncc + 3 + nextra), dim3(1024), 0, ta, h->st_cur));
   }
-  CU(cudaGetLastError());
-  if (multi) {
-    const size_t n = (size_t)h->E + COMM_SCAL + 2 * h->nranks;
-    if (h->peer_on) ST(peer_allreduce(h, 1, cc_sum_buf(h), n));
-    else ST(allreduce(h, cc_sum_buf(h), n, ncclSum_));
-  }
-  {
+  if (!fused) {
+    if (multi) ST(allreduce(h, cc_sum_buf(h), (size_t)h->E + COMM_SCAL + 2 * h->nranks, ncclSum_));
     KScope ks(h, KC_REDUCE);
-    CU(launch_k(h, k_scatter_cc, dim3(1), dim3(1024), 0, h->C, h->E, h->d_cc.p, cc_sum_buf(h), h->d_col_param.p, h->d_camp[which].p, h->d_Hcc2[bo].p, h->d_gc2[bo].p, h->d_scal.p + 8,
-                                             h->nranks, h->d_scal.p, fail_ptr(h), h->decide, h->st_cur));
+    CU(launch_k(h, k_scatter_cc, dim3(1), dim3(1024), 0, sc, h->st_cur));
   }
   CU(cudaGetLastError());
   return MCC_OK;
@@ -1232,16 +1251,24 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     CU(cudaGetLastError());
     const int n = h->npairs * SY_T * SY_T;
     {
-      KScope ks(h, KC_REDUCE);
-      CU(launch_k(h, k_reduce_rows, dim3((n + RR_E - 1) / RR_E), dim3(RR_E * RR_S), 0, h->sy_gx, n, h->d_S_part.p, S_sum_buf(h), h->st_cur));
+      // with peer windows the sum over the ranks (exchange 0) happens inside the row reduction
+      PeerEx px;
+      std::memset(&px, 0, sizeof(px));
+      px.pw.nranks = 1;
+      const bool peer = h->nranks > 1 && h->peer_on;
+      if (peer) {
+        if ((size_t)n > h->peer_nS) return fail(h, MCC_ERR_NCCL, "peer window laid out for another size");
+        px = peer_ex(h, 0);
+      }
+      KScope ks(h, peer ? KC_EXCHANGE : KC_REDUCE);
+      CU(launch_k(h, k_reduce_rows, dim3((n + RR_E - 1) / RR_E), dim3(RR_E * RR_S), 0, h->sy_gx, n, h->d_S_part.p, S_sum_buf(h), px, fail_ptr(h), h->st_cur));
     }
     CU(cudaGetLastError());
-    if (h->peer_on) ST(peer_allreduce(h, 0, S_sum_buf(h), n));
-    else ST(allreduce(h, S_sum_buf(h), n, ncclSum_));
+    if (h->nranks > 1 && !h->peer_on) ST(allreduce(h, S_sum_buf(h), n, ncclSum_));
   }
   {
     const size_t need = ((size_t)C * (C + 1) / 2 + C + 1) * sizeof(double);   // packed lower triangle + rhs row
-    const bool packed = need <= 196 * 1024;   // + ~30 KB of static shared memory in k_solve_cam
+    const bool packed = need <= 184 * 1024;   // + ~42 KB of static shared memory in k_solve_cam
     {
       KScope ks(h, KC_SOLVE);
       if (packed)
@@ -1279,20 +1306,26 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
     return MCC_OK;
   }
   ST(launch_cost(h, cand, o.use_loss, h->d_newcost_f.p, nullptr));
-  jobs.j[0] = ReduceJob{h->d_newcost_f.p, 0, nullptr};
-  jobs.j[1] = ReduceJob{h->d_mcc_f.p, 0, nullptr};
-  jobs.j[2] = ReduceJob{h->d_dx2_f.p, 0, nullptr};
-  jobs.j[3] = ReduceJob{h->d_xn2c_f.p, 0, nullptr};
+  // several ranks: [candidate cost, model cost change, |dx|^2, |x+|^2 | failure flag per rank] summed over the ranks in ONE
+  // small exchange (peer windows or NCCL), then unpacked (flags OR-ed)
+  const bool multi = h->nranks > 1;
+  double* sm4 = multi ? h->d_small.p : nullptr;
+  if (multi) CU(cudaMemsetAsync(h->d_small.p, 0, (4 + 64) * sizeof(double), h->stream));
+  jobs.j[0] = ReduceJob{h->d_newcost_f.p, 0, multi ? sm4 + 0 : nullptr};
+  jobs.j[1] = ReduceJob{h->d_mcc_f.p, 0, multi ? sm4 + 1 : nullptr};
+  jobs.j[2] = ReduceJob{h->d_dx2_f.p, 0, multi ? sm4 + 2 : nullptr};
+  jobs.j[3] = ReduceJob{h->d_xn2c_f.p, 0, multi ? sm4 + 3 : nullptr};
+  jobs.j[4] = ReduceJob{reinterpret_cast<const double*>(fail_ptr(h)), 2, multi ? sm4 + 4 + h->rank : nullptr};
   {
     KScope ks(h, KC_REDUCE);
-    k_reduce_arrays<<<4, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p + 3);
+    k_reduce_arrays<<<multi ? 5 : 4, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p + 3);
   }
   CU(cudaGetLastError());
-  if (h->nranks > 1) {
-    NC(nccl().GroupStart());
-    ST(allreduce(h, h->d_scal.p + 3, 4, ncclSum_));
-    NC(nccl().AllReduce(fail_ptr(h), fail_ptr(h), 1, ncclInt32_, ncclMax_, h->comm, h->stream));
-    NC(nccl().GroupEnd());
+  if (multi) {
+    ST(allreduce_small(h, sm4, 4 + h->nranks));
+    KScope ks(h, KC_REDUCE);
+    k_unpack_small<<<1, 32, 0, h->stream>>>(h->nranks, sm4, h->d_scal.p + 3, fail_ptr(h));
+    CU(cudaGetLastError());
   }
   return MCC_OK;
 }
@@ -1542,7 +1575,7 @@ void mcc_destroy(mcc_handle* h) {
   DBuf<double>* dd[] = {&h->d_aos_w, &h->d_aos_i, &h->d_X, &h->d_Y, &h->d_Z, &h->d_U, &h->d_V, &h->d_res, &h->d_camp[0], &h->d_camp[1], &h->d_pose[0], &h->d_pose[1],
                         &h->d_setup, &h->d_frot, &h->d_camrec, &h->d_tile_s, &h->d_Hff2[0], &h->d_Hff2[1], &h->d_gf2[0], &h->d_gf2[1], &h->d_Hfc2[0], &h->d_Hfc2[1], &h->d_Lf, &h->d_cost_f, &h->d_gmax_f, &h->d_xn2_f, &h->d_newcost_f,
                         &h->d_mcc_f, &h->d_dx2_f, &h->d_xn2c_f, &h->d_cc_part, &h->d_cc_part2, &h->d_cc_sum, &h->d_Hcc2[0], &h->d_Hcc2[1], &h->d_gc2[0], &h->d_gc2[1], &h->d_scale_c, &h->d_scale_f, &h->d_S_part,
-                        &h->d_S_sum, &h->d_M, &h->d_yc, &h->d_ysc, &h->d_scal};
+                        &h->d_S_sum, &h->d_M, &h->d_yc, &h->d_ysc, &h->d_scal, &h->d_small};
   for (auto* b : dd) b->release();
   h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_tab.release(); h->d_col_param.release(); h->d_dist.release(); h->d_cls_li.release(); h->d_gs_tab.release();
   h->d_cams.release(); h->d_cc.release(); h->d_Linv.release(); h->d_zf.release();
@@ -1847,7 +1880,7 @@ mcc_status mcc_eval_cost(mcc_handle* h, int use_loss, double* cost) {
     k_reduce_arrays<<<1, 1024, 0, h->stream>>>(jobs, h->nslots, h->d_scal.p + 3);
   }
   CU(cudaGetLastError());
-  ST(allreduce(h, h->d_scal.p + 3, 1, ncclSum_));
+  ST(allreduce_small(h, h->d_scal.p + 3, 1));
   ST(read_scalars(h));
   *cost = h->h_scal[3];
   return MCC_OK;
