@@ -273,6 +273,9 @@ struct mcc_handle {
   int nframes = 0;
   std::vector<double> params;          // calibrator.cpp:36-46 layout
   bool params_valid = false;
+  std::vector<double> params_init;     // what initializeVariables() made of the current cameras and pose guesses (runCalibration
+  bool init_valid = false;             // starts from it every time; recomputed only when cameras or frames change)
+  PinBuf<double> pose_stage;           // pinned staging of the frame poses for the parameter upload / download
   std::string err;
   int device = -1;
 
@@ -455,6 +458,12 @@ mcc_status ensure_device(mcc_handle* h) {
 // calibrator.cpp:251-283
 void init_params(mcc_handle* h) {
   std::vector<double>& p = h->params;
+  if (h->init_valid) {      // same cameras, same pose guesses: same initial values (0.5 ms of host time per run on 10 000 frames)
+    p = h->params_init;
+    h->params_valid = true;
+    h->params_dirty = true;
+    return;
+  }
   p.clear();
   for (const CamHost& c : h->cams) {
     p.insert(p.end(), c.intr, c.intr + c.n_intr);
@@ -473,6 +482,8 @@ void init_params(mcc_handle* h) {
     h_transform_to_rvec_tvec(&h->poses[16 * (size_t)f], rt);
     p.insert(p.end(), rt, rt + 6);
   }
+  h->params_init = p;
+  h->init_valid = true;
   h->params_valid = true;
   h->params_dirty = true;
 }
@@ -885,21 +896,25 @@ mcc_status upload_params(mcc_handle* h) {
   if (!h->params_dirty) return MCC_OK;
   h->cur = 0;
   if (h->C_full) CU(cudaMemcpyAsync(h->d_camp[0].p, h->params.data(), h->C_full * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-  std::vector<double> pose((size_t)h->nslots * 6);
+  const size_t np = (size_t)h->nslots * 6;
+  CU(cudaStreamSynchronize(h->stream));      // nothing may still be reading the staging buffer (cheap: the stream is idle between runs)
+  if (!h->pose_stage.reserve(std::max<size_t>(np, 1))) return fail(h, MCC_ERR_BAD_ARG, "out of host memory");
+  double* pose = h->pose_stage.p;
   for (int s = 0; s < h->nslots; s++) std::memcpy(&pose[(size_t)s * 6], &h->params[h->C_full + 6 * (size_t)h->slot_frame[s]], 6 * sizeof(double));
-  if (h->nslots) CU(cudaMemcpyAsync(h->d_pose[0].p, pose.data(), pose.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-  h->h2d += (h->C_full + pose.size()) * sizeof(double);
-  CU(cudaStreamSynchronize(h->stream));
+  if (h->nslots) CU(cudaMemcpyAsync(h->d_pose[0].p, pose, np * sizeof(double), cudaMemcpyHostToDevice, h->stream));   // pinned: queued, no wait
+  h->h2d += (h->C_full + np) * sizeof(double);
   h->params_dirty = false;
   return MCC_OK;
 }
 
 mcc_status download_params(mcc_handle* h) {
   if (h->C_full) CU(cudaMemcpyAsync(h->params.data(), h->d_camp[h->cur].p, h->C_full * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-  std::vector<double> pose((size_t)h->nslots * 6);
-  if (h->nslots) CU(cudaMemcpyAsync(pose.data(), h->d_pose[h->cur].p, pose.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  const size_t np = (size_t)h->nslots * 6;
+  if (!h->pose_stage.reserve(std::max<size_t>(np, 1))) return fail(h, MCC_ERR_BAD_ARG, "out of host memory");
+  double* pose = h->pose_stage.p;
+  if (h->nslots) CU(cudaMemcpyAsync(pose, h->d_pose[h->cur].p, np * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaStreamSynchronize(h->stream));
-  h->d2h += (h->C_full + pose.size()) * sizeof(double);
+  h->d2h += (h->C_full + np) * sizeof(double);
   for (int s = 0; s < h->nslots; s++) std::memcpy(&h->params[h->C_full + 6 * (size_t)h->slot_frame[s]], &pose[(size_t)s * 6], 6 * sizeof(double));
   return MCC_OK;
 }
@@ -1579,7 +1594,7 @@ void mcc_destroy(mcc_handle* h) {
   for (auto* b : dd) b->release();
   h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_tab.release(); h->d_col_param.release(); h->d_dist.release(); h->d_cls_li.release(); h->d_gs_tab.release();
   h->d_cams.release(); h->d_cc.release(); h->d_Linv.release(); h->d_zf.release();
-  h->world.release(); h->image.release();
+  h->world.release(); h->image.release(); h->pose_stage.release();
   if (h->h_scal) cudaFreeHost(h->h_scal);
   drop_iteration_graphs(h);
   if (h->d_state) { cudaFree(h->d_state); cudaFree(h->d_ticket); cudaFreeHost(h->h_rec); for (int i = 0; i < 2; i++) cudaEventDestroy(h->ev_rec[i]); }
@@ -1620,6 +1635,7 @@ mcc_status mcc_set_cameras(mcc_handle* h, int ncam, const mcc_camera* cams) {
   bool same_layout = v.size() == h->cams.size();
   for (size_t k = 0; same_layout && k < v.size(); k++) same_layout = v[k].n_dist == h->cams[k].n_dist;
   h->cams.swap(v);
+  h->init_valid = false;
   h->structure_dirty = true;
   if (!same_layout) h->params_valid = false;
   return MCC_OK;
@@ -1688,6 +1704,7 @@ mcc_status mcc_add_frames(mcc_handle* h, int nframes, int ncam, const int* npts,
   if (!h->mask_all_one) h->mask.resize(h->nobs + n, 1);
   h->nobs += n;
   h->nframes += nframes;
+  h->init_valid = false;
   h->structure_dirty = h->obs_dirty = h->mask_dirty = true;
   h->params_valid = false;
   if (direct) {
@@ -1725,6 +1742,7 @@ mcc_status mcc_clear_frames(mcc_handle* h) {
   if (!h) return MCC_ERR_BAD_ARG;
   h->npts.clear(); h->poses.clear(); h->mask.clear(); h->mask_all_one = true;
   h->nobs = 0; h->nframes = 0; h->host_count = 0; h->dev_count = 0;
+  h->init_valid = false;
   h->structure_dirty = h->obs_dirty = h->mask_dirty = true;
   h->params_valid = false;
   return MCC_OK;

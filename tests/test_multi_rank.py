@@ -14,8 +14,9 @@ WORKER = os.path.join(os.path.dirname(__file__), "multi_rank_worker.py")
 def _launch(args, nproc, port, extra_env=None):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr", "127.0.0.1",
            "--master-port", str(port), WORKER] + list(args)
-    env = dict(os.environ, OMP_NUM_THREADS="2", **(extra_env or {}))
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT, env=env)
+    # a rank that waits in a peer exchange gives up after 30 s (instead of the default 60) so that a broken job fails fast
+    env = dict(os.environ, OMP_NUM_THREADS="4", MCC_PEER_TIMEOUT_S="30", **(extra_env or {}))
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "MULTI_RANK_OK " + " ".join(args) in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
     return r.stdout
