@@ -107,6 +107,16 @@ const char* mcc_last_error(const mcc_handle* h);
 /* CUDA device ordinal this handle computes on (default: the current device at first use). */
 mcc_status mcc_set_device(mcc_handle* h, int device);
 
+/* Several GPUs behind ONE handle, one process (no reference counterpart: the reference is single-device; its caller,
+ * calibration_nodelet.cpp:196-208 / 642, is one process that calls addPoints per frame and then runCalibration, and with this
+ * call it keeps doing exactly that).  Call it before frames are added.  The handle then deals the frames out over the
+ * devices (whole frames, levelled by observation count; page-locked arrays given to mcc_add_frames go to the devices over
+ * their own PCIe links at the same time), runs every compute call on one host thread per device, and sums the reduced
+ * camera system over the devices through peer windows (cudaDeviceEnablePeerAccess; devices without peer access to each
+ * other are refused at the first computation with MCC_ERR_NCCL).  Results, parameter layout, residual and mask order are
+ * those of a single-device handle.  ndev == 1 is mcc_set_device; at most 8 devices.  Not combinable with mcc_comm_init. */
+mcc_status mcc_set_devices(mcc_handle* h, int ndev, const int* device_ids);
+
 /* Calibrator::setCameras (calibrator.cpp:225-227) */
 mcc_status mcc_set_cameras(mcc_handle* h, int ncam, const mcc_camera* cams);
 /* Calibrator::setFixAllIntrinsics (calibrator.h:22) */

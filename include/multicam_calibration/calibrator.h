@@ -4,7 +4,7 @@
 // setFixAllIntrinsics, showCameraStatus, setCameras, addPoints, runCalibration, getCalibrationResults,
 // testCalibration, removeOutliers.  Everything below the class (problem assembly, the Ceres solve) runs on the GPU
 // in libmcc.so; this header only marshals the reference's container types into flat arrays.
-// Extensions (not in the reference): summary(), lastStatus(), setDevice(), setVerbose().
+// Extensions (not in the reference): summary(), lastStatus(), setDevice(), setDevices(), setVerbose().
 #ifndef MULTICAM_CALIBRATION_B200_CALIBRATOR_H
 #define MULTICAM_CALIBRATION_B200_CALIBRATOR_H
 #include <cstdio>
@@ -166,6 +166,8 @@ class Calibrator {
   mcc_status lastStatus() const { return status_; }
   const char *lastError() const { return mcc_last_error(h_); }
   void setDevice(int d) { mcc_set_device(h_, d); }
+  // several GPUs behind this one Calibrator (before the first addPoints); the call sequence of the reference's nodelet stays as it is
+  void setDevices(const std::vector<int> &ids) { status_ = mcc_set_devices(h_, (int)ids.size(), ids.data()); }
   void setVerbose(bool v) { verbose_ = v; }
   mcc_handle *handle() { return h_; }
   std::vector<double> params() const {

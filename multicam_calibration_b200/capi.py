@@ -65,7 +65,7 @@ class Summary(C.Structure):
 
 
 # every symbol include/mcc.h declares (tests check the built library exports all of them)
-SYMBOLS = ["mcc_version", "mcc_default_options", "mcc_summary_size", "mcc_create", "mcc_destroy", "mcc_last_error", "mcc_set_device",
+SYMBOLS = ["mcc_version", "mcc_default_options", "mcc_summary_size", "mcc_create", "mcc_destroy", "mcc_last_error", "mcc_set_device", "mcc_set_devices",
            "mcc_set_cameras", "mcc_set_fix_all_intrinsics", "mcc_set_camera_flags", "mcc_add_frame", "mcc_add_frames", "mcc_clear_frames",
            "mcc_num_frames", "mcc_num_observations", "mcc_init_params", "mcc_num_params", "mcc_get_params", "mcc_set_params", "mcc_upload",
            "mcc_run", "mcc_get_camera", "mcc_num_residuals", "mcc_eval_residuals", "mcc_eval_cost", "mcc_remove_outliers", "mcc_get_mask",
@@ -105,6 +105,7 @@ def lib():
     L.mcc_destroy.argtypes = [vp]
     L.mcc_destroy.restype = None
     L.mcc_set_device.argtypes = [vp, C.c_int]
+    L.mcc_set_devices.argtypes = [vp, C.c_int, ip]
     L.mcc_set_cameras.argtypes = [vp, C.c_int, C.POINTER(McCamera)]
     L.mcc_set_fix_all_intrinsics.argtypes = [vp, C.c_int]
     L.mcc_set_camera_flags.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int]
@@ -223,11 +224,15 @@ def rvec_tvec_to_transform(v) -> np.ndarray:
 class Calibrator:
     """Host-side mirror of the reference's Calibrator over the C ABI."""
 
-    def __init__(self, device: Optional[int] = None):
+    def __init__(self, device=None):
+        """device: None (current device), an ordinal, or a list of ordinals (several GPUs behind this one handle)"""
         self._L = lib()
         self.h = C.c_void_p()
         self._check(self._L.mcc_create(C.byref(self.h)))
-        if device is not None:
+        if isinstance(device, (list, tuple)):
+            ids = np.asarray(device, dtype=np.int32)
+            self._check(self._L.mcc_set_devices(self.h, len(ids), _ip(ids)))
+        elif device is not None:
             self._check(self._L.mcc_set_device(self.h, int(device)))
         self.cameras: List[Camera] = []
         self.summary: Optional[Summary] = None
@@ -404,7 +409,7 @@ class Calibrator:
         return int(self._L.mcc_comm_transport(self.h))
 
 
-def calibrator_from_rig(rig: Rig, device: Optional[int] = None) -> Calibrator:
+def calibrator_from_rig(rig: Rig, device=None) -> Calibrator:
     cal = Calibrator(device)
     cal.setCameras(rig.cameras)
     cal.setFixAllIntrinsics(rig.fix_all_intrinsics)

@@ -31,7 +31,7 @@ using namespace multicam_calibration;
 static void usage() {
   std::fprintf(stderr,
                "usage: mcc_calibrate --calib initial.yaml --corners corners.csv [--init-poses poses.txt] [--output out.yaml]\n"
-               "                     [--outlier-pixel-threshold px] [--fix-intrinsics] [--device n] [--residuals-dir dir]\n"
+               "                     [--outlier-pixel-threshold px] [--fix-intrinsics] [--device n | --devices 0,1,...] [--residuals-dir dir]\n"
                "                     [--latest-link name.yaml] [--quiet]\n"
                "                     [--stage 'cam0:fix_intrinsics=0,fix_extrinsics=1,active=1;cam1:active=0'] ...\n"
                "  every --stage sets camera flags (the nodelet's set_parameter service) and runs the calibrate() sequence once;\n"
@@ -86,6 +86,7 @@ int main(int argc, char **argv) {
   double outlier = -1.0;
   bool fix_intr = false, quiet = false;
   int device = -1;
+  std::vector<int> devices;      // --devices 0,1,...: several GPUs behind the one Calibrator
   for (int i = 1; i < argc; i++) {
     const std::string a = argv[i];
     auto next = [&]() -> std::string { if (i + 1 >= argc) { usage(); std::exit(2); } return argv[++i]; };
@@ -96,6 +97,11 @@ int main(int argc, char **argv) {
     else if (a == "--outlier-pixel-threshold") outlier = std::atof(next().c_str());
     else if (a == "--fix-intrinsics") fix_intr = true;
     else if (a == "--device") device = std::atoi(next().c_str());
+    else if (a == "--devices") {
+      const std::string l = next();
+      size_t p = 0;
+      while (p < l.size()) { devices.push_back(std::atoi(l.c_str() + p)); p = l.find(',', p); if (p == std::string::npos) break; p++; }
+    }
     else if (a == "--residuals-dir") residuals_dir = next();
     else if (a == "--latest-link") latest_link = next();
     else if (a == "--quiet") quiet = true;
@@ -116,7 +122,10 @@ int main(int argc, char **argv) {
   if (cameras.empty()) return 1;
 
   Calibrator cal;
-  if (device >= 0) cal.setDevice(device);
+  if (!devices.empty()) {
+    cal.setDevices(devices);
+    if (cal.lastStatus() != MCC_OK) { std::fprintf(stderr, "--devices: %s\n", cal.lastError()); return 1; }
+  } else if (device >= 0) cal.setDevice(device);
   cal.setVerbose(!quiet);
   cal.setFixAllIntrinsics(fix_intr);
   cal.setCameras(cameras);

@@ -15,6 +15,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <condition_variable>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -347,8 +348,34 @@ struct mcc_handle {
   // ---- comm
   ncclComm_t comm = nullptr;
   int nranks = 1, rank = 0;
+  // ---- several devices behind ONE handle (mcc_set_devices): this handle is then only a front that deals the frames out to one
+  // member handle per device and runs them on one host thread each; a member finds its peers through `member_of`
+  struct mcc_group* group = nullptr;      // front
+  struct mcc_group* member_of = nullptr;  // member
 
   int ncam() const { return (int)cams.size(); }
+};
+
+// The members of a multi-device handle and what they need to meet each other inside one process.
+struct mcc_group {
+  std::vector<mcc_handle*> kids;
+  std::vector<int> frame_kid, frame_local;          // per frame of the front: which member holds it, and as which of its frames
+  std::vector<std::vector<int>> kid_frames;         // per member: its frames (front numbering), in the member's order
+  std::vector<long long> kid_obs;                   // observations per member (balance)
+  bool cams_dirty = true, params_pushed = false;
+  // rendezvous of the member threads (peer-window set-up): a counting barrier and a table of window addresses
+  std::mutex mu;
+  std::condition_variable cv;
+  int arrived = 0;
+  long generation = 0;
+  std::vector<void*> win;
+  int bad = 0;
+  void barrier() {
+    std::unique_lock<std::mutex> lk(mu);
+    const long g = generation;
+    if (++arrived == (int)kids.size()) { arrived = 0; generation++; cv.notify_all(); }
+    else cv.wait(lk, [&] { return generation != g; });
+  }
 };
 
 namespace {
@@ -1019,8 +1046,9 @@ void free_peer_window(mcc_handle* h) {
   // solve or evaluation: an exchange returns on this rank only once EVERY rank's cells of that exchange have arrived, and
   // a peer stores into this window again only in a later exchange, i.e. in a later call that this rank takes part in.
   cudaStreamSynchronize(h->stream);
-  for (int r = 0; r < h->pw.nranks; r++)
-    if (r != h->pw.rank && h->pw.base[r]) cudaIpcCloseMemHandle(h->pw.base[r]);
+  if (!h->member_of)
+    for (int r = 0; r < h->pw.nranks; r++)
+      if (r != h->pw.rank && h->pw.base[r]) cudaIpcCloseMemHandle(h->pw.base[r]);
   cudaFree(h->peer_own);
   h->peer_own = nullptr; h->peer_on = false; h->peer_nS = h->peer_nC = 0;
   h->pw = PeerWin{};
@@ -1032,12 +1060,52 @@ void free_peer_window(mcc_handle* h) {
 mcc_status ensure_peer_window(mcc_handle* h) {
   if (h->nranks <= 1) return MCC_OK;
   const char* env = std::getenv("MCC_P2P");
-  if ((env && env[0] == '0') || h->nranks > PEER_MAX) return MCC_OK;
+  if (((env && env[0] == '0') && !h->member_of) || h->nranks > PEER_MAX) return MCC_OK;   // (members of one handle have no NCCL to fall back to)
   const size_t nS = (size_t)h->npairs * SY_T * SY_T, nC = (size_t)h->E + COMM_SCAL + 2 * 64;
   if ((h->peer_own || h->peer_failed) && h->peer_nS == nS && h->peer_nC == nC) return MCC_OK;
   free_peer_window(h);
   h->peer_failed = false;
   const int R = h->nranks;
+  if (h->member_of) {
+    // Members of a multi-device handle live in one process: no CUDA IPC, no NCCL.  Every member allocates its window,
+    // enables peer access to the other devices and publishes the address; two barriers of the member threads replace the
+    // two agreement all-reduces.  All members call this at the same time (the front runs them on a thread each).
+    mcc_group* g = h->member_of;
+    const size_t cells_ip = 2 * (size_t)R * (nS + nC + PEER_SMALL);
+    int bad_ip = 0;
+    if (cudaMalloc((void**)&h->peer_own, cells_ip * sizeof(uint4)) != cudaSuccess) { h->peer_own = nullptr; bad_ip = 1; }
+    if (!bad_ip && cudaMemsetAsync(h->peer_own, 0, cells_ip * sizeof(uint4), h->stream) != cudaSuccess) bad_ip = 1;
+    for (int r = 0; r < R && !bad_ip; r++) {
+      if (r == h->rank) continue;
+      int can = 0;
+      if (cudaDeviceCanAccessPeer(&can, h->device, g->kids[r]->device) != cudaSuccess || !can) { bad_ip = 1; break; }
+      const cudaError_t pe = cudaDeviceEnablePeerAccess(g->kids[r]->device, 0);
+      if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) bad_ip = 1;
+    }
+    if (cudaStreamSynchronize(h->stream) != cudaSuccess) bad_ip = 1;
+    cudaGetLastError();
+    { std::lock_guard<std::mutex> lk(g->mu); g->win[h->rank] = h->peer_own; if (h->rank == 0) g->bad = 0; }
+    g->barrier();
+    { std::lock_guard<std::mutex> lk(g->mu); g->bad |= bad_ip; }
+    g->barrier();
+    const int any_bad = g->bad;
+    PeerWin pwi{};
+    pwi.nranks = R; pwi.rank = h->rank;
+    for (int r = 0; r < R; r++) pwi.base[r] = (uint4*)g->win[r];
+    g->barrier();            // everybody has read the table and the verdict before anybody may start the next round
+    h->peer_nS = nS; h->peer_nC = nC;
+    if (any_bad) {
+      if (h->peer_own) cudaFree(h->peer_own);
+      h->peer_own = nullptr; h->pw = PeerWin{}; h->peer_on = false; h->peer_failed = true;
+      return fail(h, MCC_ERR_NCCL, "no peer access between the devices of this multi-device handle (device %d)", h->device);
+    }
+    h->pw = pwi;
+    h->peer_seq[0] = h->peer_seq[1] = h->peer_seq[2] = 0; h->peer_on = true;
+    double secs = 60.0;
+    if (const char* e = std::getenv("MCC_PEER_TIMEOUT_S")) { const double v = std::atof(e); if (v > 0.0) secs = v; }
+    h->peer_timeout_cycles = (long long)(secs * 2.0e9);
+    return MCC_OK;
+  }
   const size_t cells = 2 * (size_t)R * (nS + nC + PEER_SMALL);   // 2 parities x R slots per exchange class, 16 bytes per value
   int bad = 0;
   if (cudaMalloc((void**)&h->peer_own, cells * sizeof(uint4)) != cudaSuccess) { h->peer_own = nullptr; bad = 1; }
@@ -1548,6 +1616,246 @@ mcc_status solve(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
 
 }  // namespace
 
+
+// =================================================================================================
+// Several devices behind one handle (mcc_set_devices).  The front handle keeps what the reference's Calibrator keeps
+// about the problem as a whole (cameras, point counts, pose guesses, the parameter vector in the reference's layout) and
+// deals the frames out to one member handle per device; every compute call runs the members on one host thread each.
+// The members are ordinary handles with nranks = number of devices: they shard the solve exactly like the
+// one-process-per-GPU mode, but find each other's peer windows inside the process (ensure_peer_window).
+// =================================================================================================
+namespace {
+
+template <typename F>
+mcc_status group_each(mcc_handle* h, F fn) {
+  std::vector<mcc_handle*>& K = h->group->kids;
+  std::vector<mcc_status> st(K.size(), MCC_OK);
+  std::vector<std::thread> th;
+  for (size_t r = 0; r < K.size(); r++) th.emplace_back([&, r] { st[r] = fn(K[r], (int)r); });
+  for (std::thread& t : th) t.join();
+  for (size_t r = 0; r < K.size(); r++)
+    if (st[r] != MCC_OK) return fail(h, st[r], "device %d: %s", K[r]->device, K[r]->err.c_str());
+  return MCC_OK;
+}
+
+mcc_status group_push_cameras(mcc_handle* h) {
+  mcc_group* g = h->group;
+  if (!g->cams_dirty) return MCC_OK;
+  std::vector<mcc_camera> cams(h->cams.size());
+  for (size_t k = 0; k < h->cams.size(); k++) {
+    const CamHost& c = h->cams[k];
+    mcc_camera& m = cams[k];
+    m.model = c.model; m.n_intr = c.n_intr; m.n_dist = c.n_dist; m.intr = c.intr; m.dist = c.dist;
+    std::memcpy(m.T_cn_cnm1, c.T, sizeof(m.T_cn_cnm1));
+    m.fix_intr = c.fix_intr; m.fix_extr = c.fix_extr; m.active = c.active;
+  }
+  for (mcc_handle* k : g->kids) {
+    mcc_status st = mcc_set_cameras(k, (int)cams.size(), cams.data());
+    if (st == MCC_OK) st = mcc_set_fix_all_intrinsics(k, h->fix_all ? 1 : 0);
+    if (st != MCC_OK) return fail(h, st, "device %d: %s", k->device, k->err.c_str());
+  }
+  g->cams_dirty = false;
+  return MCC_OK;
+}
+
+// the front's parameter vector (reference layout, all frames) -> every member's vector (its frames only)
+mcc_status group_push_params(mcc_handle* h) {
+  mcc_group* g = h->group;
+  if (g->params_pushed || !h->params_valid) return MCC_OK;
+  const size_t ncp = h->params.size() - 6 * (size_t)h->nframes;
+  for (size_t r = 0; r < g->kids.size(); r++) {
+    std::vector<double> p(h->params.begin(), h->params.begin() + ncp);
+    for (int f : g->kid_frames[r]) p.insert(p.end(), h->params.begin() + ncp + 6 * (size_t)f, h->params.begin() + ncp + 6 * (size_t)f + 6);
+    const mcc_status st = mcc_set_params(g->kids[r], p.data(), p.size());
+    if (st != MCC_OK) return fail(h, st, "device %d: %s", g->kids[r]->device, g->kids[r]->err.c_str());
+  }
+  g->params_pushed = true;
+  return MCC_OK;
+}
+
+// every member's vector -> the front's; the camera part must be the same bits on every member
+mcc_status group_pull_params(mcc_handle* h) {
+  mcc_group* g = h->group;
+  const long long np = mcc_num_params(h);
+  const size_t ncp = (size_t)np - 6 * (size_t)h->nframes;
+  h->params.assign((size_t)np, 0.0);
+  for (size_t r = 0; r < g->kids.size(); r++) {
+    const std::vector<double>& p = g->kids[r]->params;
+    if (p.size() != ncp + 6 * g->kid_frames[r].size()) return fail(h, MCC_ERR_NUMERICAL, "device %d holds %zu parameters, expected %zu", g->kids[r]->device, p.size(), ncp + 6 * g->kid_frames[r].size());
+    if (r == 0) std::memcpy(h->params.data(), p.data(), ncp * sizeof(double));
+    else if (std::memcmp(h->params.data(), p.data(), ncp * sizeof(double)) != 0) return fail(h, MCC_ERR_NUMERICAL, "the devices disagree on the camera parameters (device %d)", g->kids[r]->device);
+    for (size_t i = 0; i < g->kid_frames[r].size(); i++) std::memcpy(&h->params[ncp + 6 * (size_t)g->kid_frames[r][i]], &p[ncp + 6 * i], 6 * sizeof(double));
+  }
+  h->params_valid = true;
+  g->params_pushed = true;
+  return MCC_OK;
+}
+
+mcc_status group_add_frames(mcc_handle* h, int nframes, int ncam, const int* npts, const double* world_xyz, const double* image_uv, const double* poses) {
+  mcc_group* g = h->group;
+  ST(group_push_cameras(h));
+  const int n = (int)g->kids.size();
+  std::vector<long long> fobs(nframes), off(nframes + 1, 0);
+  for (int f = 0; f < nframes; f++) {
+    long long c = 0;
+    for (int k = 0; k < ncam; k++) { if (npts[(size_t)f * ncam + k] < 0) return fail(h, MCC_ERR_BAD_ARG, "negative point count"); c += npts[(size_t)f * ncam + k]; }
+    fobs[f] = c; off[f + 1] = off[f] + c;
+  }
+  if (off[nframes] && (!world_xyz || !image_uv)) return fail(h, MCC_ERR_BAD_ARG, "null point arrays");
+  // who gets which frames of this batch: contiguous pieces that level the members' observation counts; a batch
+  // smaller than the member count goes frame by frame to whoever holds the least
+  std::vector<int> piece_lo(n, 0), piece_hi(n, 0);
+  std::vector<int> single_owner;
+  if (nframes >= n) {
+    long long total = off[nframes];
+    for (long long v : g->kid_obs) total += v;
+    int f = 0;
+    long long have_all = 0, want_all = 0;
+    for (int r = 0; r < n; r++) {
+      piece_lo[r] = f;
+      want_all += (total + n - 1 - r) / n;                     // cumulative target after member r
+      have_all += g->kid_obs[r];
+      while (f < nframes && (r == n - 1 || have_all + fobs[f] / 2 < want_all)) { have_all += fobs[f]; f++; }
+      piece_hi[r] = f;
+    }
+  } else {
+    std::vector<long long> load = g->kid_obs;
+    for (int f = 0; f < nframes; f++) {
+      int best = 0;
+      for (int r = 1; r < n; r++) if (load[r] < load[best]) best = r;
+      single_owner.push_back(best);
+      load[best] += fobs[f];
+    }
+  }
+  auto add_piece = [&](int r, int lo, int hi) -> mcc_status {
+    if (hi <= lo) return MCC_OK;
+    return mcc_add_frames(g->kids[r], hi - lo, ncam, npts + (size_t)lo * ncam, world_xyz ? world_xyz + 3 * off[lo] : nullptr,
+                          image_uv ? image_uv + 2 * off[lo] : nullptr, poses + 16 * (size_t)lo);
+  };
+  if (nframes >= n) {
+    // one host thread per member: page-locked caller arrays go to the devices over their own PCIe links at the same time
+    ST(group_each(h, [&](mcc_handle*, int r) { return add_piece(r, piece_lo[r], piece_hi[r]); }));
+  } else {
+    for (int f = 0; f < nframes; f++) {
+      const mcc_status st = add_piece(single_owner[f], f, f + 1);
+      if (st != MCC_OK) return fail(h, st, "device %d: %s", g->kids[single_owner[f]]->device, g->kids[single_owner[f]]->err.c_str());
+    }
+  }
+  // bookkeeping of the front
+  const int f0 = h->nframes;
+  g->frame_kid.resize(f0 + nframes); g->frame_local.resize(f0 + nframes);
+  auto own = [&](int f, int r) {
+    g->frame_kid[f0 + f] = r; g->frame_local[f0 + f] = (int)g->kid_frames[r].size();
+    g->kid_frames[r].push_back(f0 + f); g->kid_obs[r] += fobs[f];
+  };
+  if (nframes >= n) { for (int r = 0; r < n; r++) for (int f = piece_lo[r]; f < piece_hi[r]; f++) own(f, r); }
+  else for (int f = 0; f < nframes; f++) own(f, single_owner[f]);
+  h->npts.insert(h->npts.end(), npts, npts + (size_t)nframes * ncam);
+  h->poses.insert(h->poses.end(), poses, poses + 16 * (size_t)nframes);
+  h->nobs += (size_t)off[nframes];
+  h->nframes += nframes;
+  h->init_valid = false;
+  h->params_valid = false;
+  g->params_pushed = false;
+  return MCC_OK;
+}
+
+mcc_status group_run(mcc_handle* h, const mcc_options& o, mcc_summary& S) {
+  mcc_group* g = h->group;
+  const double t0 = now_s();
+  ST(group_push_cameras(h));
+  if (o.keep_params) {
+    if (!h->params_valid) init_params(h);
+    ST(group_push_params(h));
+  }
+  if (o.verbose) std::printf("Num params: %lld\nNum residuals: %lld\n", mcc_num_params(h), mcc_num_residuals(h));
+  std::vector<mcc_summary> sums(g->kids.size());
+  ST(group_each(h, [&](mcc_handle* k, int r) {
+    mcc_options ok = o;
+    if (r != 0) ok.verbose = 0;
+    return mcc_run(k, &ok, &sums[r]);
+  }));
+  ST(group_pull_params(h));
+  S = sums[0];
+  const int Cc = mcc_num_reduced_cam_cols(h);
+  S.num_params = (int)h->params.size();
+  S.num_residuals = 0; S.num_reduced_params = Cc; S.n_kernel_launches = 0; S.h2d_bytes = 0; S.d2h_bytes = 0;
+  for (const mcc_summary& s : sums) {
+    S.num_residuals += s.num_residuals; S.num_reduced_params += s.num_reduced_params - Cc;
+    S.n_kernel_launches += s.n_kernel_launches; S.h2d_bytes += s.h2d_bytes; S.d2h_bytes += s.d2h_bytes;
+  }
+  S.t_total = now_s() - t0;
+  return MCC_OK;
+}
+
+// per frame of the front: residual doubles it contributes (valid points of active cameras x 2), from the members' masks
+mcc_status group_frame_residual_counts(mcc_handle* h, std::vector<long long>& cnt) {
+  mcc_group* g = h->group;
+  const int ncam = h->ncam();
+  cnt.assign(h->nframes, 0);
+  for (size_t r = 0; r < g->kids.size(); r++) {
+    mcc_handle* k = g->kids[r];
+    std::vector<uint8_t> m(k->nobs + 1);
+    if (mcc_get_mask(k, m.data(), k->nobs) != MCC_OK) return fail(h, MCC_ERR_BAD_ARG, "mask of device %d", k->device);
+    size_t o = 0;
+    for (int f : g->kid_frames[r])
+      for (int c = 0; c < ncam; c++) {
+        const int np = h->npts[(size_t)f * ncam + c];
+        if (h->cams[c].active) for (int i = 0; i < np; i++) cnt[f] += 2 * (m[o + i] != 0);
+        o += np;
+      }
+  }
+  return MCC_OK;
+}
+
+mcc_status group_eval_residuals(mcc_handle* h, double* out_xy, size_t n_out) {
+  mcc_group* g = h->group;
+  ST(group_push_cameras(h));
+  ST(group_push_params(h));
+  std::vector<std::vector<double>> buf(g->kids.size());
+  ST(group_each(h, [&](mcc_handle* k, int r) {
+    const long long n = mcc_num_residuals(k);
+    buf[r].assign((size_t)std::max<long long>(n, 1), 0.0);
+    return mcc_eval_residuals(k, buf[r].data(), (size_t)n);
+  }));
+  std::vector<long long> cnt;
+  ST(group_frame_residual_counts(h, cnt));
+  long long total = 0;
+  for (long long c : cnt) total += c;
+  if ((long long)n_out < total) return fail(h, MCC_ERR_BAD_ARG, "output too small: need %lld doubles", total);
+  std::vector<size_t> cur(g->kids.size(), 0);
+  size_t w = 0;
+  for (int f = 0; f < h->nframes; f++) {          // frame order of the front; a member's stream is in ITS frame order, which is ascending too
+    const int r = g->frame_kid[f];
+    std::memcpy(out_xy + w, buf[r].data() + cur[r], (size_t)cnt[f] * sizeof(double));
+    w += (size_t)cnt[f]; cur[r] += (size_t)cnt[f];
+  }
+  return MCC_OK;
+}
+
+// mask of the front's observation order <-> the members' (dir 0: gather into out, 1: scatter from in)
+mcc_status group_mask(mcc_handle* h, uint8_t* out, const uint8_t* in) {
+  mcc_group* g = h->group;
+  const int ncam = h->ncam();
+  std::vector<size_t> fo(h->nframes + 1, 0);
+  for (int f = 0; f < h->nframes; f++) { size_t c = 0; for (int k = 0; k < ncam; k++) c += h->npts[(size_t)f * ncam + k]; fo[f + 1] = fo[f] + c; }
+  for (size_t r = 0; r < g->kids.size(); r++) {
+    mcc_handle* k = g->kids[r];
+    std::vector<uint8_t> m(k->nobs + 1);
+    if (out && mcc_get_mask(k, m.data(), k->nobs) != MCC_OK) return fail(h, MCC_ERR_BAD_ARG, "mask of device %d", k->device);
+    size_t o = 0;
+    for (int f : g->kid_frames[r]) {
+      const size_t n = fo[f + 1] - fo[f];
+      if (out) std::memcpy(out + fo[f], m.data() + o, n); else std::memcpy(m.data() + o, in + fo[f], n);
+      o += n;
+    }
+    if (in && k->nobs && mcc_set_mask(k, m.data(), k->nobs) != MCC_OK) return fail(h, MCC_ERR_BAD_ARG, "mask of device %d", k->device);
+  }
+  return MCC_OK;
+}
+
+}  // namespace
+
 // =================================================================================================
 // C ABI
 // =================================================================================================
@@ -1583,6 +1891,13 @@ mcc_status mcc_create(mcc_handle** out) {
 
 void mcc_destroy(mcc_handle* h) {
   if (!h) return;
+  if (h->group) {
+    for (mcc_handle* k : h->group->kids) mcc_destroy(k);
+    delete h->group;
+    h->world.release(); h->image.release(); h->pose_stage.release();
+    delete h;
+    return;
+  }
   if (h->device >= 0) cudaSetDevice(h->device);
   free_peer_window(h);
   if (h->comm && nccl().has_windows()) free_comm_windows(h);
@@ -1607,8 +1922,34 @@ void mcc_destroy(mcc_handle* h) {
 
 const char* mcc_last_error(const mcc_handle* h) { return h ? h->err.c_str() : "null handle"; }
 
+mcc_status mcc_set_devices(mcc_handle* h, int ndev, const int* ids) {
+  if (!h || ndev < 1 || !ids) return fail(h, MCC_ERR_BAD_ARG, "bad device list");
+  if (h->group) return fail(h, MCC_ERR_BAD_ARG, "devices already set for this handle");
+  if (h->stream || h->nframes) return fail(h, MCC_ERR_BAD_ARG, "set the devices before frames are added and before the first computation");
+  if (ndev == 1) return mcc_set_device(h, ids[0]);
+  if (ndev > PEER_MAX) return fail(h, MCC_ERR_BAD_ARG, "at most %d devices per handle", PEER_MAX);
+  int have = 0;
+  if (cudaGetDeviceCount(&have) != cudaSuccess || have == 0) { cudaGetLastError(); return fail(h, MCC_ERR_NO_DEVICE, "no CUDA device available; this library has no CPU fallback"); }
+  for (int i = 0; i < ndev; i++) {
+    if (ids[i] < 0 || ids[i] >= have) return fail(h, MCC_ERR_BAD_ARG, "device %d does not exist (%d devices)", ids[i], have);
+    for (int j = 0; j < i; j++) if (ids[j] == ids[i]) return fail(h, MCC_ERR_BAD_ARG, "device %d listed twice", ids[i]);
+  }
+  mcc_group* g = new (std::nothrow) mcc_group();
+  if (!g) return MCC_ERR_BAD_ARG;
+  for (int r = 0; r < ndev; r++) {
+    mcc_handle* k = nullptr;
+    if (mcc_create(&k) != MCC_OK) { for (mcc_handle* q : g->kids) mcc_destroy(q); delete g; return fail(h, MCC_ERR_BAD_ARG, "out of memory"); }
+    k->device = ids[r]; k->nranks = ndev; k->rank = r; k->member_of = g;
+    g->kids.push_back(k);
+  }
+  g->kid_frames.resize(ndev); g->kid_obs.assign(ndev, 0); g->win.assign(ndev, nullptr);
+  h->group = g;
+  return MCC_OK;
+}
+
 mcc_status mcc_set_device(mcc_handle* h, int device) {
   if (!h) return MCC_ERR_BAD_ARG;
+  if (h->group) return fail(h, MCC_ERR_BAD_ARG, "devices already set for this handle");
   if (h->stream) return fail(h, MCC_ERR_BAD_ARG, "device already in use by this handle");
   h->device = device;
   return MCC_OK;
@@ -1636,6 +1977,7 @@ mcc_status mcc_set_cameras(mcc_handle* h, int ncam, const mcc_camera* cams) {
   for (size_t k = 0; same_layout && k < v.size(); k++) same_layout = v[k].n_dist == h->cams[k].n_dist;
   h->cams.swap(v);
   h->init_valid = false;
+  if (h->group) { h->group->cams_dirty = true; h->group->params_pushed = false; }
   h->structure_dirty = true;
   if (!same_layout) h->params_valid = false;
   return MCC_OK;
@@ -1645,6 +1987,7 @@ mcc_status mcc_set_fix_all_intrinsics(mcc_handle* h, int fix) {
   if (!h) return MCC_ERR_BAD_ARG;
   h->fix_all = fix != 0;
   h->structure_dirty = true;
+  if (h->group) h->group->cams_dirty = true;
   return MCC_OK;
 }
 
@@ -1652,6 +1995,9 @@ mcc_status mcc_set_camera_flags(mcc_handle* h, int cam, int fix_intr, int fix_ex
   if (!h || cam < 0 || cam >= h->ncam()) return fail(h, MCC_ERR_BAD_ARG, "bad camera index");
   h->cams[cam].fix_intr = fix_intr; h->cams[cam].fix_extr = fix_extr; h->cams[cam].active = active;
   h->structure_dirty = true;
+  if (h->group)
+    for (mcc_handle* k : h->group->kids)
+      if (!h->group->cams_dirty) ST(mcc_set_camera_flags(k, cam, fix_intr, fix_extr, active));
   return MCC_OK;
 }
 
@@ -1662,6 +2008,7 @@ mcc_status mcc_add_frames(mcc_handle* h, int nframes, int ncam, const int* npts,
     return fail(h, MCC_ERR_BAD_ARG, "number of cams != width of array!");
   }
   if (nframes < 0 || !npts || !poses) return fail(h, MCC_ERR_BAD_ARG, "null argument");
+  if (h->group) return group_add_frames(h, nframes, ncam, npts, world_xyz, image_uv, poses);
   size_t n = 0;
   for (size_t i = 0; i < (size_t)nframes * ncam; i++) { if (npts[i] < 0) return fail(h, MCC_ERR_BAD_ARG, "negative point count"); n += npts[i]; }
   if (n && (!world_xyz || !image_uv)) return fail(h, MCC_ERR_BAD_ARG, "null point arrays");
@@ -1740,6 +2087,14 @@ mcc_status mcc_add_frame(mcc_handle* h, int ncam, const int* npts, const double*
 
 mcc_status mcc_clear_frames(mcc_handle* h) {
   if (!h) return MCC_ERR_BAD_ARG;
+  if (h->group) {
+    mcc_group* g = h->group;
+    for (mcc_handle* k : g->kids) mcc_clear_frames(k);
+    g->frame_kid.clear(); g->frame_local.clear();
+    for (auto& v : g->kid_frames) v.clear();
+    std::fill(g->kid_obs.begin(), g->kid_obs.end(), 0);
+    g->params_pushed = false;
+  }
   h->npts.clear(); h->poses.clear(); h->mask.clear(); h->mask_all_one = true;
   h->nobs = 0; h->nframes = 0; h->host_count = 0; h->dev_count = 0;
   h->init_valid = false;
@@ -1761,6 +2116,7 @@ long long mcc_num_params(const mcc_handle* h) {
 
 mcc_status mcc_init_params(mcc_handle* h) {
   if (!h) return MCC_ERR_BAD_ARG;
+  if (h->group) h->group->params_pushed = false;
   init_params(h);
   return MCC_OK;
 }
@@ -1779,11 +2135,18 @@ mcc_status mcc_set_params(mcc_handle* h, const double* in, size_t n) {
   h->params.assign(in, in + n);
   h->params_valid = true;
   h->params_dirty = true;
+  if (h->group) h->group->params_pushed = false;
   return MCC_OK;
 }
 
 mcc_status mcc_upload(mcc_handle* h) {
   if (!h) return MCC_ERR_BAD_ARG;
+  if (h->group) {
+    if (h->cams.empty() || h->nframes == 0) return fail(h, MCC_ERR_NO_DATA, "no data to run on!");
+    ST(group_push_cameras(h));
+    ST(group_push_params(h));
+    return group_each(h, [](mcc_handle* k, int) { return mcc_upload(k); });
+  }
   ST(prepare(h));
   CU(cudaStreamSynchronize(h->stream));
   return MCC_OK;
@@ -1802,6 +2165,7 @@ mcc_status mcc_run(mcc_handle* h, const mcc_options* opts, mcc_summary* out) {
     S.termination = 2; S.why = 7;
     return fail(h, MCC_ERR_NO_DATA, "no data to run on!");
   }
+  if (h->group) return group_run(h, o, S);
   const double t0 = now_s();
   const long long l0 = h->launches, u0 = h->h2d, d0 = h->d2h;
   if (!o.keep_params) init_params(h);
@@ -1810,7 +2174,7 @@ mcc_status mcc_run(mcc_handle* h, const mcc_options* opts, mcc_summary* out) {
   S.num_params = (int)h->params.size();
   S.num_reduced_params = h->C + 6 * h->nslots;
   S.num_residuals = h->nres;
-  if (o.verbose) std::printf("Num params: %d\nNum residuals: %lld\n", S.num_params, S.num_residuals);
+  if (o.verbose && !h->member_of) std::printf("Num params: %d\nNum residuals: %lld\n", S.num_params, S.num_residuals);   // (a multi-device front prints the totals)
   if (h->nslots == 0 && h->nranks <= 1) { S.termination = 2; S.why = 7; return fail(h, MCC_ERR_NO_DATA, "no valid points in any active camera"); }
   mcc_status st = solve(h, o, S);
   if (st != MCC_OK) return st;
@@ -1849,6 +2213,7 @@ mcc_status mcc_get_camera(const mcc_handle* hc, int k, double* intr, double* dis
 long long mcc_num_residuals(const mcc_handle* hc) {
   mcc_handle* h = const_cast<mcc_handle*>(hc);
   if (!h) return 0;
+  if (h->group) { long long t = 0; for (mcc_handle* k : h->group->kids) t += mcc_num_residuals(k); return t; }
   long long n = 0;
   size_t o = 0;
   for (int f = 0; f < h->nframes; f++)
@@ -1862,6 +2227,7 @@ long long mcc_num_residuals(const mcc_handle* hc) {
 
 mcc_status mcc_eval_residuals(mcc_handle* h, double* out_xy, size_t n_out) {
   if (!h || !out_xy) return MCC_ERR_BAD_ARG;
+  if (h->group) return group_eval_residuals(h, out_xy, n_out);
   ST(prepare(h));
   if ((long long)n_out < h->nres) return fail(h, MCC_ERR_BAD_ARG, "output too small: need %lld doubles", h->nres);
   CU(h->d_res.reserve(2 * std::max<size_t>(h->nobs, 1)));
@@ -1888,6 +2254,14 @@ mcc_status mcc_eval_residuals(mcc_handle* h, double* out_xy, size_t n_out) {
 
 mcc_status mcc_eval_cost(mcc_handle* h, int use_loss, double* cost) {
   if (!h || !cost) return MCC_ERR_BAD_ARG;
+  if (h->group) {
+    ST(group_push_cameras(h));
+    ST(group_push_params(h));
+    std::vector<double> c(h->group->kids.size(), 0.0);
+    ST(group_each(h, [&](mcc_handle* k, int r) { return mcc_eval_cost(k, use_loss, &c[r]); }));   // every member returns the sum over all
+    *cost = c[0];
+    return MCC_OK;
+  }
   ST(prepare(h));
   ST(launch_cost(h, h->cur, use_loss, h->d_newcost_f.p, nullptr));
   ReduceJobs jobs;
@@ -1906,6 +2280,16 @@ mcc_status mcc_eval_cost(mcc_handle* h, int use_loss, double* cost) {
 
 mcc_status mcc_remove_outliers(mcc_handle* h, double max_err, long long* ndropped) {
   if (!h) return MCC_ERR_BAD_ARG;
+  if (h->group) {
+    ST(group_push_cameras(h));
+    ST(group_push_params(h));
+    std::vector<long long> d(h->group->kids.size(), 0);
+    ST(group_each(h, [&](mcc_handle* k, int r) { return mcc_remove_outliers(k, max_err, &d[r]); }));
+    long long t = 0;
+    for (long long v : d) t += v;
+    if (ndropped) *ndropped = t;
+    return MCC_OK;
+  }
   ST(prepare(h));
   CU(h->d_res.reserve(2 * std::max<size_t>(h->nobs, 1)));
   ST(launch_cost(h, h->cur, 0, nullptr, h->d_res.p));
@@ -1937,12 +2321,14 @@ mcc_status mcc_remove_outliers(mcc_handle* h, double max_err, long long* ndroppe
 
 mcc_status mcc_get_mask(const mcc_handle* h, uint8_t* out, size_t n) {
   if (!h || !out || n < h->nobs) return MCC_ERR_BAD_ARG;
+  if (h->group) return group_mask(const_cast<mcc_handle*>(h), out, nullptr);
   if (h->mask_all_one) std::memset(out, 1, h->nobs);
   else std::memcpy(out, h->mask.data(), h->nobs);
   return MCC_OK;
 }
 mcc_status mcc_set_mask(mcc_handle* h, const uint8_t* in, size_t n) {
   if (!h || !in || n != h->nobs) return MCC_ERR_BAD_ARG;
+  if (h->group) return group_mask(h, nullptr, in);
   materialize_mask(h);
   std::memcpy(h->mask.data(), in, n);
   h->mask_all_one = false;
@@ -1958,10 +2344,15 @@ int mcc_num_reduced_cam_cols(const mcc_handle* hc) {
   for (int k = 1; k < h->ncam(); k++) if (!h->cams[k].fix_extr) C += 6;
   return C;
 }
-long long mcc_num_active_frames(const mcc_handle* h) { return h ? h->nslots : 0; }
+long long mcc_num_active_frames(const mcc_handle* h) {
+  if (!h) return 0;
+  if (h->group) { long long t = 0; for (mcc_handle* k : h->group->kids) t += k->nslots; return t; }
+  return h->nslots;
+}
 
 mcc_status mcc_eval_normal_blocks(mcc_handle* h, int use_loss, double* cost, double* Hcc, double* gc, double* Hff, double* gf, double* Hfc, int* frame_ids) {
   if (!h) return MCC_ERR_BAD_ARG;
+  if (h->group) return fail(h, MCC_ERR_BAD_ARG, "the block test hook works on single-device handles");
   ST(prepare(h));
   ST(launch_jacobian(h, use_loss, h->cur, h->blk));
   ST(read_scalars(h));
@@ -1987,6 +2378,7 @@ mcc_status mcc_comm_unique_id(unsigned char id[MCC_UNIQUE_ID_BYTES]) {
 
 mcc_status mcc_comm_init(mcc_handle* h, int nranks, int rank, const unsigned char id[MCC_UNIQUE_ID_BYTES]) {
   if (!h || !id || nranks < 1 || rank < 0 || rank >= nranks) return fail(h, MCC_ERR_BAD_ARG, "bad communicator arguments");
+  if (h->group || h->member_of) return fail(h, MCC_ERR_BAD_ARG, "a multi-device handle shards inside the process; one process per GPU uses single-device handles");
   if (nranks == 1) { h->nranks = 1; h->rank = 0; drop_iteration_graphs(h); return MCC_OK; }
   if (nranks > 64) return fail(h, MCC_ERR_BAD_ARG, "at most 64 ranks (per-rank slots of the merged all-reduce)");
   if (!nccl().ok()) return fail(h, MCC_ERR_NCCL, "libnccl.so.2 not found");
@@ -2000,12 +2392,14 @@ mcc_status mcc_comm_init(mcc_handle* h, int nranks, int rank, const unsigned cha
 }
 
 int mcc_comm_transport(const mcc_handle* h) {
+  if (h && h->group) return mcc_comm_transport(h->group->kids[0]);
   if (!h || h->nranks <= 1) return 0;
   return h->peer_on ? 1 : 2;
 }
 
 mcc_status mcc_set_kernel_timing(mcc_handle* h, int enabled) {
   if (!h) return MCC_ERR_BAD_ARG;
+  if (h->group) { for (mcc_handle* k : h->group->kids) mcc_set_kernel_timing(k, enabled); return MCC_OK; }
   h->ktiming = enabled != 0;
   for (int i = 0; i < KC_COUNT; i++) { h->kc_ms[i] = 0.0; h->kc_n[i] = 0; }
   return MCC_OK;
@@ -2019,6 +2413,7 @@ const char* mcc_kernel_class_name(int c) {
 
 mcc_status mcc_get_kernel_times(mcc_handle* h, double* ms, long long* counts, int n) {
   if (!h || n < KC_COUNT) return MCC_ERR_BAD_ARG;
+  if (h->group) return mcc_get_kernel_times(h->group->kids[0], ms, counts, n);      // the first device's
   if (h->stream) { CU(cudaStreamSynchronize(h->stream)); resolve_ktiming(h); }
   for (int i = 0; i < KC_COUNT; i++) { if (ms) ms[i] = h->kc_ms[i]; if (counts) counts[i] = h->kc_n[i]; }
   return MCC_OK;
@@ -2026,6 +2421,7 @@ mcc_status mcc_get_kernel_times(mcc_handle* h, double* ms, long long* counts, in
 
 mcc_status mcc_timer_start(mcc_handle* h) {
   if (!h) return MCC_ERR_BAD_ARG;
+  if (h->group) return mcc_timer_start(h->group->kids[0]);
   ST(ensure_device(h));
   if (!h->tm_a) { CU(cudaEventCreate(&h->tm_a)); CU(cudaEventCreate(&h->tm_b)); }
   CU(cudaStreamSynchronize(h->stream));
@@ -2034,6 +2430,7 @@ mcc_status mcc_timer_start(mcc_handle* h) {
 }
 
 mcc_status mcc_timer_stop(mcc_handle* h, double* ms) {
+  if (h && h->group) return mcc_timer_stop(h->group->kids[0], ms);
   if (!h || !ms || !h->tm_a) return MCC_ERR_BAD_ARG;
   CU(cudaEventRecord(h->tm_b, h->stream));
   CU(cudaEventSynchronize(h->tm_b));

@@ -6,7 +6,7 @@
 //   rig file:  ncam nframes
 //              per camera: model n_dist fx fy cx cy d0..d{n-1}  T(16)  fix_intr fix_extr active
 //              per frame:  T_c0_w(16)  then per camera: n  followed by n lines "x y z u v"
-//   usage:     facade_gpu <rig file> [- [run]]
+//   usage:     facade_gpu <rig file> [<devices: - or e.g. 0,1> [run]]
 #include <cstdio>
 #include <cstdlib>
 #include <fstream>
@@ -40,6 +40,14 @@ int main(int argc, char **argv) {
   }
   Calibrator cal;
   cal.setVerbose(false);
+  const std::string devs = argc > 2 ? argv[2] : "-";
+  if (devs != "-") {
+    std::vector<int> ids;
+    size_t p = 0;
+    while (p < devs.size()) { ids.push_back(std::atoi(devs.c_str() + p)); p = devs.find(',', p); if (p == std::string::npos) break; p++; }
+    cal.setDevices(ids);
+    if (cal.lastStatus() != MCC_OK) { std::printf("SETDEVICES_FAILED %s\n", cal.lastError()); return 1; }
+  }
   cal.setCameras(cams);
   for (int f = 0; f < nframes; f++) {
     CameraExtrinsics T;
