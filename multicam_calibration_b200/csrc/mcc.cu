@@ -296,6 +296,8 @@ struct mcc_handle {
   DBuf<int2> d_dist;                   // hand-out lists of the Jacobian pass (per camera: pose x camera, camera x camera, pose x pose)
   DBuf<uint4> d_cls_li;                // lane records per camera class
   DBuf<double> d_Linv, d_zf;
+  bool k1_temp_global = false;         // frames too large for shared memory: their tile Grams go through d_k1_temp
+  DBuf<double> d_k1_temp;
   int ncls = 0, maxft = 1, k1_grid = 1, k1_fs = 0, cc_rows = 1;   // Jacobian pass: grid, statically dealt frames, rows of cc_part
   unsigned int* d_ticket = nullptr;    // [0] frame counter of the Jacobian pass, [1..] entry-block counters of k_reduce_misc
   DBuf<double> d_cc_part2;
@@ -831,8 +833,10 @@ mcc_status build_structure(mcc_handle* h) {
   h->sy_gx = std::max(1, std::min((h->nslots + SY_FB - 1) / SY_FB, std::max(1, (2 * sms) / h->sy_gy)));
   // the Jacobian pass: persistent CTAs, as many as fit at once (shared memory: rows of 4 warps + the frame's tile Grams)
   {
-    const size_t smem = k1_smem_bytes(h->rowstride, ncam, h->maxft);
-    if (smem > 200 * 1024) return fail(h, MCC_ERR_TOO_LARGE, "a frame with %d tiles needs %zu bytes of shared memory in the Jacobian pass", h->maxft, smem);
+    // frames whose tile Grams would take more than ~100 KB park them in global memory instead (k1_temp_global)
+    h->k1_temp_global = k1_smem_bytes(h->rowstride, ncam, h->maxft) > 100 * 1024;
+    const size_t smem = k1_smem_bytes(h->rowstride, ncam, h->k1_temp_global ? 0 : h->maxft);
+    if (smem > 200 * 1024) return fail(h, MCC_ERR_TOO_LARGE, "%d cameras need %zu bytes of shared memory in the Jacobian pass", ncam, smem);
     int occ = 0;
     if (h->rowstride == 15) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_frame_normal<15>, K1_WARPS * 32, smem));
     else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_frame_normal<21>, K1_WARPS * 32, smem));
@@ -844,6 +848,7 @@ mcc_status build_structure(mcc_handle* h) {
     if (const char* e = std::getenv("MCC_K1_STATIC_FRAC")) frac = std::min(1.0, std::max(0.0, std::atof(e)));
     h->k1_fs = (int)(frac * h->nslots / h->k1_grid) * h->k1_grid;
     h->cc_rows = h->k1_grid + (h->nslots - h->k1_fs);
+    if (h->k1_temp_global) CU(h->d_k1_temp.reserve((size_t)h->k1_grid * ((size_t)h->maxft * (h->rowstride / 3) * k1_nacc(h->rowstride) + h->maxft)));
   }
 
   // upload structure
@@ -1231,7 +1236,8 @@ mcc_status launch_jacobian(mcc_handle* h, int use_loss, int which, int bo, const
     ka.oX = h->d_X.p; ka.oY = h->d_Y.p; ka.oZ = h->d_Z.p; ka.oU = h->d_U.p; ka.oV = h->d_V.p; ka.omask = h->d_mask.p;
     ka.Hff = h->d_Hff2[bo].p; ka.gf = h->d_gf2[bo].p; ka.Hfc = h->d_Hfc2[bo].p; ka.cost_f = h->d_cost_f.p; ka.gmax_f = h->d_gmax_f.p; ka.xn2_f = h->d_xn2_f.p;
     ka.cc_part = h->d_cc_part.p; ka.st = h->st_cur; ka.fs = h->k1_fs; ka.ticket = h->d_ticket;
-    const size_t smem = k1_smem_bytes(h->rowstride, h->ncam(), h->maxft);
+    const size_t smem = k1_smem_bytes(h->rowstride, h->ncam(), h->k1_temp_global ? 0 : h->maxft);
+    ka.temp_g = h->k1_temp_global ? h->d_k1_temp.p : nullptr;
     if (!rot_ready) {     // inside an LM iteration k_solve_cam and k_backsub have already made the records of the candidate
       KScope ks(h, KC_SETUP);
       CU(launch_k(h, k_rot_setup, dim3((h->nslots + h->ncam() + 127) / 128), dim3(128), 0, h->nslots, h->ncam(), h->d_cams.p, h->d_camp[which].p, h->d_pose[which].p, h->d_frot.p,
@@ -1904,7 +1910,7 @@ void mcc_destroy(mcc_handle* h) {
   if (h->comm && nccl().CommDestroy) nccl().CommDestroy(h->comm);
   DBuf<double>* dd[] = {&h->d_aos_w, &h->d_aos_i, &h->d_X, &h->d_Y, &h->d_Z, &h->d_U, &h->d_V, &h->d_res, &h->d_camp[0], &h->d_camp[1], &h->d_pose[0], &h->d_pose[1],
                         &h->d_setup, &h->d_frot, &h->d_camrec, &h->d_tile_s, &h->d_Hff2[0], &h->d_Hff2[1], &h->d_gf2[0], &h->d_gf2[1], &h->d_Hfc2[0], &h->d_Hfc2[1], &h->d_Lf, &h->d_cost_f, &h->d_gmax_f, &h->d_xn2_f, &h->d_newcost_f,
-                        &h->d_mcc_f, &h->d_dx2_f, &h->d_xn2c_f, &h->d_cc_part, &h->d_cc_part2, &h->d_cc_sum, &h->d_Hcc2[0], &h->d_Hcc2[1], &h->d_gc2[0], &h->d_gc2[1], &h->d_scale_c, &h->d_scale_f, &h->d_S_part,
+                        &h->d_mcc_f, &h->d_dx2_f, &h->d_xn2c_f, &h->d_cc_part, &h->d_cc_part2, &h->d_k1_temp, &h->d_cc_sum, &h->d_Hcc2[0], &h->d_Hcc2[1], &h->d_gc2[0], &h->d_gc2[1], &h->d_scale_c, &h->d_scale_f, &h->d_S_part,
                         &h->d_S_sum, &h->d_M, &h->d_yc, &h->d_ysc, &h->d_scal, &h->d_small};
   for (auto* b : dd) b->release();
   h->d_mask.release(); h->d_tiles.release(); h->d_gto.release(); h->d_tab.release(); h->d_col_param.release(); h->d_dist.release(); h->d_cls_li.release(); h->d_gs_tab.release();

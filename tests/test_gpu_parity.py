@@ -288,6 +288,34 @@ def test_pinned_and_pageable_inputs_agree(small_rig, c3_rig):
     cal.close(); ref.close()
 
 
+def test_frames_with_thousands_of_points(built):
+    """a frame whose tiles do not fit the Jacobian pass's shared memory (30 000 points of one camera = 188 tiles) takes the
+    global-memory parking of the tile Grams: same blocks, same solve as the oracle"""
+    from multicam_calibration_b200 import synth
+    from multicam_calibration_b200.rig import Camera, Rig
+    rng = np.random.default_rng(12)
+    cam = Camera("equidistant", np.array([600.0, 601.0, 640.0, 512.0]), np.array([-0.0147, 0.0004, -0.004, 0.0015]))
+    worlds, images, poses = [], [], []
+    for f in range(3):
+        n = 30000 if f < 2 else 500
+        w = np.concatenate([rng.uniform(-0.3, 0.3, (n, 2)), np.zeros((n, 1))], axis=1)
+        T = np.eye(4)
+        T[:3, :3] = synth.rodrigues(np.array([0.11 - 0.1 * f, -0.07, 0.2 * f]))
+        T[:3, 3] = [0.02, -0.03, 0.7 + 0.1 * f]
+        uv = synth.project("equidistant", w @ T[:3, :3].T + T[:3, 3], cam.intrinsics, cam.distortion_coeffs) + rng.normal(0, 0.3, (n, 2))
+        Tg = T.copy()
+        Tg[:3, 3] += [0.004, -0.003, 0.006]               # start a little off
+        worlds.append(w); images.append(uv); poses.append(Tg)
+    start = Camera("equidistant", cam.intrinsics * 1.002, cam.distortion_coeffs + 1e-4)
+    rig = Rig([start], np.array([[30000], [30000], [500]], dtype=np.int32), np.concatenate(worlds), np.concatenate(images), np.array(poses))
+    cal, orc = _pair(rig)
+    g, o = cal.normalBlocks(True), orc.normal_blocks(True)
+    for key in ("Hcc", "gc", "Hff", "gf", "Hfc"):
+        assert _rel(g[key], o[key]) <= 1e-10, (key, _rel(g[key], o[key]))
+    _check_solve(cal, orc)
+    cal.close()
+
+
 def test_full_size_c4_properties(built):
     """config c4 at BASELINE.json's full size (8 cameras, 10 000 frames, ~20 M residuals, 60 106 parameters): too big
     for the oracle in a test, so size-independent properties are checked instead"""
