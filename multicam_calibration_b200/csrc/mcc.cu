@@ -2413,7 +2413,7 @@ mcc_status mcc_set_kernel_timing(mcc_handle* h, int enabled) {
 
 int mcc_num_kernel_classes(void) { return KC_COUNT; }
 const char* mcc_kernel_class_name(int c) {
-  static const char* names[KC_COUNT] = {"group_setup", "tile_normal", "frame_assemble", "schur_syrk", "solve_cam", "backsub", "tile_cost", "reduce", "other", "exchange"};
+  static const char* names[KC_COUNT] = {"setup", "frame_normal", "frame_assemble", "schur_syrk", "solve_cam", "backsub", "tile_cost", "reduce", "other", "exchange"};
   return (c >= 0 && c < KC_COUNT) ? names[c] : "";
 }
 

@@ -1,5 +1,5 @@
 """Host logic of the tile kernel's contraction (no GPU): the block-pair units and the lane -> (unit, row slice) map that
-build_structure() hands to k_tile_normal, through the mcc_debug_lane_map test hook."""
+build_structure() hands to k_frame_normal, through the mcc_debug_lane_map test hook."""
 import ctypes as C
 
 import numpy as np
