@@ -85,6 +85,16 @@ def build(force: bool = False) -> str:
     return LIB_PATH
 
 
+ASAN_LIB_PATH = os.path.join(_HERE, "libmcc_asan.so")
+
+
+def build_sanitized() -> str:
+    """the same sources with the host code under AddressSanitizer + UBSan (test infrastructure: tests/test_sanitizers.py)"""
+    src_dir = os.path.join(_HERE, "csrc")
+    subprocess.check_call(["make", "-C", src_dir, "-s", "asan"])
+    return ASAN_LIB_PATH
+
+
 _lib = None
 
 
