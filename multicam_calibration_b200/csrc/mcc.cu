@@ -1314,11 +1314,6 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
   const int C = h->C;
   if (!h->st_cur) CU(cudaMemsetAsync(fail_ptr(h), 0, sizeof(int), h->stream));   // queued iterations: decide_body clears the flags
   {
-    if (h->nslots) {
-      KScope ks(h, KC_SCHUR);
-      CU(launch_k(h, k_frame_chol, dim3((h->nslots + 127) / 128), dim3(128), 0, h->nslots, radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hff2[h->blk].p, h->d_gf2[h->blk].p, h->d_scale_f.p,
-                                                                    h->d_Lf.p, h->d_Linv.p, h->d_zf.p, fail_ptr(h), h->st_cur));
-    }
     CU(cudaGetLastError());
     auto schur_smem = [&](int fb, bool pf) {
       size_t b = ((size_t)fb * 6 * h->LD + 2 * fb * (36 + 18)) * sizeof(double);
@@ -1330,7 +1325,8 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
       KScope ks(h, KC_SCHUR);
 #define MCC_LAUNCH_SCHUR(PF, FB)                                                                                                                   \
       CU((launch_k(h, k_schur_syrk<PF, FB>, grid, dim3(SY_THREADS), schur_smem(FB, PF), h->nslots, C, h->LD, h->npairs, h->d_Hfc2[h->blk].p, h->d_scale_f.p,     \
-                                                                                h->d_scale_c.p, h->d_Lf.p, h->d_Linv.p, h->d_zf.p, h->d_S_part.p, h->st_cur)))
+                                                                                h->d_scale_c.p, h->d_Lf.p, h->d_Linv.p, h->d_zf.p, h->d_S_part.p,                                \
+                                                                                radius, o.min_lm_diagonal, o.max_lm_diagonal, h->d_Hff2[h->blk].p, h->d_gf2[h->blk].p, fail_ptr(h), h->st_cur)))
       // prefetch variants keep two CTAs per SM (<= 112 KB each): 8 frames per batch, else 4; wider systems read Hfc from global memory
       if (schur_smem(8, true) <= 112 * 1024) MCC_LAUNCH_SCHUR(true, 8);
       else if (schur_smem(4, true) <= 112 * 1024) MCC_LAUNCH_SCHUR(true, 4);
@@ -1374,7 +1370,7 @@ mcc_status launch_step(mcc_handle* h, const mcc_options& o, double radius, bool 
   if (h->nslots) {
     {
       KScope ks(h, KC_BACKSUB);
-      CU(launch_k(h, k_backsub, dim3((h->nslots + 3) / 4), dim3(128), 0, h->nslots, C, h->d_Hff2[h->blk].p, h->d_gf2[h->blk].p, h->d_Hfc2[h->blk].p, h->d_Lf.p, h->d_scale_f.p, h->d_ysc.p,
+      CU(launch_k(h, k_backsub, dim3((h->nslots + 3) / 4), dim3(128), 0, h->nslots, C, h->d_Hff2[h->blk].p, h->d_gf2[h->blk].p, h->d_Hfc2[h->blk].p, h->d_Lf.p, h->d_Linv.p, h->d_scale_f.p, h->d_ysc.p,
                                                          h->d_pose[cur].p, h->d_pose[cand].p, h->d_mcc_f.p, h->d_dx2_f.p, h->d_xn2c_f.p, fail_ptr(h), h->d_frot.p, h->st_cur));
     }
     CU(cudaGetLastError());
