@@ -246,6 +246,21 @@ mcc_status mcc_reprojection_cost_noalloc(int model, int n_dist, const double* d_
 mcc_status mcc_init_pose(int model, const double* intr, int n_dist, const double* dist, int npts, const double* world_xyz,
                          const double* image_uv, double* T_cam_world);
 
+/* The same for many views at once: the views are independent (one per (frame, camera) that saw the board -- the nodelet
+ * computes one per camera per frame, calibration_nodelet.cpp:510-543), so they are spread over host threads.  A 10 000-frame,
+ * 8-camera corners file is 80 000 views: ~16 s on one core, ~1 s on sixteen.  T_cam_world: n_views x 16 doubles, row-major; a
+ * view that fails gets the zero matrix (what get_init_pose returns, get_init_pose.cpp:88) and its status in status[v] (may
+ * be NULL).  n_threads <= 0: one per hardware thread.  Returns MCC_OK unless an argument is invalid: per-view failures are not
+ * an error of the call.  Results are bit-identical to n_views calls of mcc_init_pose, whatever the thread count. */
+typedef struct mcc_view {
+  int model, n_dist, npts;
+  const double* intr;        /* fx fy cx cy */
+  const double* dist;        /* n_dist coefficients */
+  const double* world_xyz;   /* npts x 3 */
+  const double* image_uv;    /* npts x 2 */
+} mcc_view;
+mcc_status mcc_init_pose_batch(int n_views, const mcc_view* views, double* T_cam_world, mcc_status* status, int n_threads);
+
 /* Transform helpers used by the facade: Eigen AngleAxisd(R) route of transform_to_rvec_tvec
  * (calibrator.cpp:157-170) and utils::rotation_matrix (utils.h:29-39). */
 void mcc_transform_to_rvec_tvec(const double T[16], double out6[6]);

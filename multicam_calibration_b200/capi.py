@@ -37,6 +37,13 @@ class McCamera(C.Structure):
                 ("T_cn_cnm1", C.c_double * 16), ("fix_intr", C.c_int), ("fix_extr", C.c_int), ("active", C.c_int)]
 
 
+class View(C.Structure):
+    """mcc_view (include/mcc.h)"""
+    _fields_ = [("model", C.c_int), ("n_dist", C.c_int), ("npts", C.c_int),
+                ("intr", C.POINTER(C.c_double)), ("dist", C.POINTER(C.c_double)),
+                ("world_xyz", C.POINTER(C.c_double)), ("image_uv", C.POINTER(C.c_double))]
+
+
 class Options(C.Structure):
     _fields_ = [("max_num_iterations", C.c_int),
                 ("function_tolerance", C.c_double), ("parameter_tolerance", C.c_double), ("gradient_tolerance", C.c_double),
@@ -72,7 +79,7 @@ SYMBOLS = ["mcc_version", "mcc_default_options", "mcc_summary_size", "mcc_create
            "mcc_set_mask", "mcc_num_reduced_cam_cols", "mcc_num_active_frames", "mcc_eval_normal_blocks", "mcc_comm_unique_id", "mcc_comm_init", "mcc_comm_transport",
            "mcc_transform_to_rvec_tvec", "mcc_rvec_tvec_to_transform", "mcc_timer_start", "mcc_timer_stop", "mcc_set_kernel_timing",
            "mcc_num_kernel_classes", "mcc_kernel_class_name", "mcc_get_kernel_times", "mcc_measure_fp64_peak", "mcc_debug_lane_map",
-           "mcc_reprojection_cost_noalloc", "mcc_init_pose"]
+           "mcc_reprojection_cost_noalloc", "mcc_init_pose", "mcc_init_pose_batch"]
 
 
 def build(force: bool = False) -> str:
@@ -153,6 +160,7 @@ def lib():
     L.mcc_get_kernel_times.argtypes = [vp, dp, C.POINTER(C.c_longlong), C.c_int]
     L.mcc_measure_fp64_peak.argtypes = [C.c_int, dp]
     L.mcc_init_pose.argtypes = [C.c_int, dp, C.c_int, dp, C.c_int, dp, dp, dp]
+    L.mcc_init_pose_batch.argtypes = [C.c_int, C.POINTER(View), dp, ip, C.c_int]
     L.mcc_reprojection_cost_noalloc.argtypes = [C.c_int, C.c_int] + [vp, vp, C.c_size_t] + [vp] * 8 + [C.c_char_p, C.c_size_t]
     assert L.mcc_summary_size() == C.sizeof(Summary), (L.mcc_summary_size(), C.sizeof(Summary))
     _lib = L
@@ -215,6 +223,27 @@ def init_pose(camera: Camera, world_xyz: np.ndarray, image_uv: np.ndarray) -> np
     if st != 0:
         raise MccError(st, "mcc_init_pose failed")
     return T.reshape(4, 4)
+
+
+def init_pose_batch(views, n_threads: int = 0):
+    """mcc_init_pose_batch: views = [(camera, world_points Nx3, image_points Nx2), ...] -> (T [n,4,4], status [n])"""
+    n = len(views)
+    arr = (View * max(n, 1))()
+    keep = []
+    for i, (camera, w, im) in enumerate(views):
+        w = np.ascontiguousarray(w, dtype=np.float64)
+        im = np.ascontiguousarray(im, dtype=np.float64)
+        intr = np.ascontiguousarray(camera.intrinsics, dtype=np.float64)
+        dist = np.ascontiguousarray(camera.distortion_coeffs, dtype=np.float64)
+        keep.append((w, im, intr, dist))
+        arr[i].model, arr[i].n_dist, arr[i].npts = camera.model_id, len(dist), len(w)
+        arr[i].intr, arr[i].dist, arr[i].world_xyz, arr[i].image_uv = _dp(intr), _dp(dist), _dp(w), _dp(im)
+    T = np.zeros((n, 16))
+    status = np.zeros(n, dtype=np.int32)
+    st = lib().mcc_init_pose_batch(n, arr, _dp(T), _ip(status), n_threads)
+    if st != 0:
+        raise MccError(st, "mcc_init_pose_batch failed")
+    return T.reshape(n, 4, 4), status
 
 
 def transform_to_rvec_tvec(T) -> np.ndarray:

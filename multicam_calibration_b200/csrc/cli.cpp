@@ -32,10 +32,11 @@ static void usage() {
   std::fprintf(stderr,
                "usage: mcc_calibrate --calib initial.yaml --corners corners.csv [--init-poses poses.txt] [--output out.yaml]\n"
                "                     [--outlier-pixel-threshold px] [--fix-intrinsics] [--device n | --devices 0,1,...] [--residuals-dir dir]\n"
-               "                     [--latest-link name.yaml] [--quiet]\n"
+               "                     [--latest-link name.yaml] [--quiet] [--init-poses-out poses.txt] [--pose-threads n] [--dry-run]\n"
                "                     [--stage 'cam0:fix_intrinsics=0,fix_extrinsics=1,active=1;cam1:active=0'] ...\n"
                "  every --stage sets camera flags (the nodelet's set_parameter service) and runs the calibrate() sequence once;\n"
-               "  the result of a stage is the starting point of the next (example_calib_manager.py); no --stage: one run\n");
+               "  the result of a stage is the starting point of the next (example_calib_manager.py); no --stage: one run\n"
+               "  --init-poses-out writes the initial cam0 poses (the format --init-poses reads); --dry-run stops after them\n");
 }
 
 // calibration_nodelet.cpp:292-345
@@ -81,7 +82,9 @@ static std::string reprojection_report(Calibrator &cal, const CalibDataVec &cali
 }
 
 int main(int argc, char **argv) {
-  std::string calib, corners, poses_file, output, residuals_dir, latest_link;
+  std::string calib, corners, poses_file, poses_out, output, residuals_dir, latest_link;
+  bool dry_run = false;
+  int pose_threads = 0;
   std::vector<std::string> stages;
   double outlier = -1.0;
   bool fix_intr = false, quiet = false;
@@ -93,6 +96,9 @@ int main(int argc, char **argv) {
     if (a == "--calib") calib = next();
     else if (a == "--corners") corners = next();
     else if (a == "--init-poses") poses_file = next();
+    else if (a == "--init-poses-out") poses_out = next();
+    else if (a == "--pose-threads") pose_threads = std::atoi(next().c_str());
+    else if (a == "--dry-run") dry_run = true;
     else if (a == "--output") output = next();
     else if (a == "--outlier-pixel-threshold") outlier = std::atof(next().c_str());
     else if (a == "--fix-intrinsics") fix_intr = true;
@@ -155,12 +161,23 @@ int main(int argc, char **argv) {
       f++;
     }
   }
+  // no file: the reference's guessCameraPose for every frame, all views at once over the host's threads (get_init_pose.h)
+  if (poses_file.empty()) have = guessCameraPoses(cameras, worldPoints, imagePoints, &poses, pose_threads);
+  if (!poses_out.empty()) {
+    // what --init-poses reads back: one line per frame, 16 numbers row-major, "nan" for a frame without a pose
+    std::ofstream po(poses_out);
+    po.precision(17);
+    for (size_t f = 0; f < nframes; f++) {
+      if (!have[f]) { po << "nan\n"; continue; }
+      for (int i = 0; i < 16; i++) po << poses[f].data()[i] << (i == 15 ? "\n" : " ");
+    }
+  }
+  if (dry_run) { std::printf("dry run: initial poses of %zu frames, no solve\n", nframes); return 0; }
   std::vector<size_t> frame_of_added;
   for (size_t f = 0; f < nframes; f++) {
     CamWorldPoints wp; CamImagePoints ip;
     bool any = false;
     for (size_t k = 0; k < cameras.size(); k++) { wp.push_back(worldPoints[k][f]); ip.push_back(imagePoints[k][f]); any = any || !wp.back().empty(); }
-    if (any && poses_file.empty()) have[f] = guessCameraPose(cameras, wp, ip, &poses[f], (int)f);
     if (!any || !have[f]) { std::printf("no detections found, skipping frame %zu\n", f); continue; }
     cal.addPoints((int)f, wp, ip, poses[f]);
     frame_of_added.push_back(f);

@@ -14,6 +14,9 @@
 #include <cmath>
 #include <cstring>
 #include <vector>
+#include <thread>
+#include <atomic>
+#include <algorithm>
 
 #include "../../include/mcc.h"
 
@@ -219,5 +222,31 @@ extern "C" mcc_status mcc_init_pose(int model, const double* intr, int n_dist, c
     T_cam_world[i * 4 + 3] = H[i * 3 + 2];
   }
   T_cam_world[12] = T_cam_world[13] = T_cam_world[14] = 0.0; T_cam_world[15] = 1.0;
+  return MCC_OK;
+}
+
+// many views at once: independent, so they are dealt to host threads by a shared counter
+extern "C" mcc_status mcc_init_pose_batch(int n_views, const mcc_view* views, double* T_cam_world, mcc_status* status, int n_threads) {
+  if (n_views < 0 || (n_views && (!views || !T_cam_world))) return MCC_ERR_BAD_ARG;
+  if (n_threads <= 0) n_threads = (int)std::max(1u, std::thread::hardware_concurrency());
+  n_threads = std::min(n_threads, std::max(1, n_views / 16));      // not worth a thread for a handful of views
+  std::atomic<int> next(0);
+  auto work = [&]() {
+    for (;;) {
+      const int v0 = next.fetch_add(16);
+      if (v0 >= n_views) break;
+      for (int v = v0; v < std::min(n_views, v0 + 16); v++) {
+        const mcc_view& w = views[v];
+        double* T = T_cam_world + (size_t)v * 16;
+        const mcc_status st = mcc_init_pose(w.model, w.intr, w.n_dist, w.dist, w.npts, w.world_xyz, w.image_uv, T);
+        if (st != MCC_OK) std::memset(T, 0, 16 * sizeof(double));
+        if (status) status[v] = st;
+      }
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < n_threads; t++) pool.emplace_back(work);
+  work();
+  for (auto& th : pool) th.join();
   return MCC_OK;
 }

@@ -10,6 +10,7 @@
 
 #include "multicam_calibration/calibrator.h"
 #include "multicam_calibration/corners_csv.h"
+#include "multicam_calibration/get_init_pose.h"
 #include "multicam_calibration/kalibr_yaml.h"
 
 using namespace multicam_calibration;
@@ -160,6 +161,49 @@ int main(int argc, char **argv) {
   Calibrator cal2;
   cal2.setCameras(bv);
   CHECK(cal2.lastStatus() == MCC_ERR_BAD_MODEL);
+  {
+    // guessCameraPose (calibration_nodelet.cpp:510-543) frame by frame against guessCameraPoses over all frames at once:
+    // two undistorted pinhole cameras 0.2 m apart looking at a 7 x 5 board; camera 0 misses the board in every third frame
+    CalibDataVec two(2);
+    for (int k = 0; k < 2; k++) {
+      two[k].name = "cam" + std::to_string(k);
+      two[k].intrinsics.distortion_model = k ? "radtan" : "equidistant";
+      two[k].intrinsics.intrinsics = {600.0, 600.0, 640.0, 512.0};
+      two[k].intrinsics.distortion_coeffs = {0.0, 0.0, 0.0, 0.0};
+      two[k].T_cn_cnm1 = identity();
+    }
+    two[1].T_cn_cnm1(0, 3) = -0.2;
+    const int NF = 40;
+    std::vector<CamWorldPoints> W(2, CamWorldPoints(NF));
+    std::vector<CamImagePoints> I(2, CamImagePoints(NF));
+    for (int f = 0; f < NF; f++) {
+      const double a = 0.02 * f - 0.3, tz = 1.0 + 0.01 * f;          // board rotated about y, in front of the cameras
+      for (int k = 0; k < 2; k++) {
+        if (k == 0 && f % 3 == 2) continue;
+        for (int i = 0; i < 35; i++) {
+          const double X = 0.05 * (i % 7) - 0.15, Y = 0.05 * (i / 7) - 0.1;
+          const double xc = std::cos(a) * X + (k ? -0.2 : 0.0), yc = Y, zc = -std::sin(a) * X + tz;
+          double u = xc / zc, v = yc / zc;
+          if (k == 0) { const double r = std::sqrt(u * u + v * v), th = std::atan(r); const double sc = r > 0 ? th / r : 1.0; u *= sc; v *= sc; }
+          W[k][f].emplace_back(X, Y, 0.0);
+          I[k][f].emplace_back(600.0 * u + 640.0, 600.0 * v + 512.0);
+        }
+      }
+    }
+    std::vector<CameraExtrinsics> batch;
+    const std::vector<bool> have = guessCameraPoses(two, W, I, &batch, 3);
+    CHECK(have.size() == (size_t)NF && batch.size() == (size_t)NF);
+    for (int f = 0; f < NF; f++) {
+      CamWorldPoints wp = {W[0][f], W[1][f]};
+      CamImagePoints ip = {I[0][f], I[1][f]};
+      CameraExtrinsics one;
+      const bool ok = guessCameraPose(two, wp, ip, &one, f);
+      CHECK(ok && have[f]);
+      for (int i = 0; i < 16; i++) CHECK(one.data()[i] == batch[f].data()[i]);      // the same arithmetic, bit for bit
+      const double a = 0.02 * f - 0.3;
+      CHECK(std::fabs(one(0, 0) - std::cos(a)) < 1e-4 && std::fabs(one(2, 0) + std::sin(a)) < 1e-4 && std::fabs(one(2, 3) - (1.0 + 0.01 * f)) < 1e-3 && std::fabs(one(0, 3)) < 1e-3);
+    }
+  }
   std::printf("FACADE_OK\n");
   return 0;
 }
